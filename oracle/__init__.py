@@ -1,0 +1,185 @@
+"""CPU oracle for the NLOS transient renderer -- TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs may import this package.  The product (nlos_gaussian_renderer_b200) never does.
+
+numpy in / numpy out wrappers over oracle/_build/libnlos_oracle.so (nlos_oracle.c).
+`precision` is "f32" (faithful fp32 restatement of the reference CUDA kernels) or
+"f64" (same formulas evaluated in double; culling stays fp32).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+_LIB = None
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = C.CDLL(_build.build())
+        _LIB.orc_det_expf.restype = C.c_float
+        _LIB.orc_det_expf.argtypes = [C.c_float]
+        _LIB.orc_num_threads.restype = C.c_int
+    return _LIB
+
+
+def _f(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def num_threads():
+    return int(lib().orc_num_threads())
+
+
+def set_num_threads(n):
+    lib().orc_set_num_threads(C.c_int(int(n)))
+
+
+def det_expf(x):
+    x = _f(x)
+    out = np.empty_like(x)
+    l = lib()
+    flat, oflat = x.reshape(-1), out.reshape(-1)
+    for i in range(flat.size):
+        oflat[i] = l.orc_det_expf(C.c_float(float(flat[i])))
+    return out
+
+
+def bboxes(means, log_scales, rots, scaling_modifier=1.0, sigma=3.0, exp_mode=1):
+    """bbox_compute.cuh:23-120 -> [N,6] (min xyz, max xyz)."""
+    means, log_scales, rots = _f(means), _f(log_scales), _f(rots)
+    N = means.shape[0]
+    out = np.empty((N, 6), np.float32)
+    lib().orc_bboxes(_p(means), _p(log_scales), _p(rots), C.c_int(N), C.c_float(scaling_modifier),
+                     C.c_float(sigma), C.c_int(exp_mode), _p(out))
+    return out
+
+
+def filter_gaussians(ray_o, ray_d, bbox, cap=256):
+    """ray_aabb.cu:10-102 -> int32 [n_rays, cap+1] (col 0 = count, unused = -1)."""
+    ray_o, ray_d, bbox = _f(ray_o), _f(ray_d), _f(bbox).reshape(-1, 6)
+    n_rays, N = ray_o.shape[0], bbox.shape[0]
+    out = np.empty((n_rays, cap + 1), np.int32)
+    lib().orc_filter(_p(ray_o), _p(ray_d), _p(bbox), C.c_int(n_rays), C.c_int(N), C.c_int(cap), _p(out))
+    return out
+
+
+def _rt(precision):
+    return (np.float32, "orc32_") if precision == "f32" else (np.float64, "orc64_")
+
+
+def render_rays(ray_o, ray_d, t_samples, means, log_scales, rots, opac, feats, cam,
+                sh_degree=0, c=1.0, deltaT=0.01, scaling_modifier=1.0, use_occlusion=True,
+                cap=256, mode=0, exp_mode=1, precision="f32", filter_lists=None):
+    """volume_renderer.cu:189-305.  cap<=0: every Gaussian passing the slab test (no 256 cap).
+    Returns rho_density, density, transmittance each [n_rays, T]."""
+    ray_o, ray_d, t_samples = _f(ray_o), _f(ray_d), _f(t_samples)
+    means, log_scales, rots, opac, feats, cam = _f(means), _f(log_scales), _f(rots), _f(opac).reshape(-1), _f(feats), _f(cam)
+    n_rays, T, N = ray_o.shape[0], t_samples.shape[0], means.shape[0]
+    feats = feats.reshape(N, -1)
+    dt, pre = _rt(precision)
+    bb = bboxes(means, log_scales, rots, scaling_modifier, 3.0, exp_mode)
+    if cap > 0 and filter_lists is None:
+        filter_lists = filter_gaussians(ray_o, ray_d, bb, cap)
+    if filter_lists is not None:
+        filter_lists = np.ascontiguousarray(filter_lists, np.int32)
+        cap = filter_lists.shape[1] - 1
+    outs = [np.zeros((n_rays, T), dt) for _ in range(3)]
+    getattr(lib(), pre + "render_rays")(
+        _p(ray_o), _p(ray_d), _p(t_samples), _p(filter_lists), C.c_int(cap), _p(bb),
+        _p(means), _p(log_scales), _p(rots), _p(opac), _p(feats), _p(cam),
+        C.c_int(n_rays), C.c_int(T), C.c_int(N), C.c_int(sh_degree), C.c_int(feats.shape[1]),
+        C.c_float(c), C.c_float(deltaT), C.c_float(scaling_modifier), C.c_int(int(use_occlusion)),
+        C.c_int(mode), C.c_int(exp_mode), _p(outs[0]), _p(outs[1]), _p(outs[2]))
+    return tuple(outs)
+
+
+def render_rays_analytic(ray_o, ray_d, t_min, t_max, filter_lists, means, log_scales, rots, opac, feats, cam,
+                         sh_degree=0, scaling_modifier=1.0, sigma_threshold=3.0, max_sections=128,
+                         exp_mode=1, precision="f32"):
+    """volume_renderer_analytic.cu:23-241 -> [n_rays]."""
+    ray_o, ray_d = _f(ray_o), _f(ray_d)
+    means, log_scales, rots, opac, feats, cam = _f(means), _f(log_scales), _f(rots), _f(opac).reshape(-1), _f(feats), _f(cam)
+    n_rays, N = ray_o.shape[0], means.shape[0]
+    feats = feats.reshape(N, -1)
+    filter_lists = np.ascontiguousarray(filter_lists, np.int32)
+    cap = filter_lists.shape[1] - 1
+    dt, pre = _rt(precision)
+    out = np.zeros((n_rays,), dt)
+    getattr(lib(), pre + "render_rays_analytic")(
+        _p(ray_o), _p(ray_d), C.c_float(t_min), C.c_float(t_max), _p(filter_lists), C.c_int(cap),
+        _p(means), _p(log_scales), _p(rots), _p(opac), _p(feats), _p(cam),
+        C.c_int(n_rays), C.c_int(N), C.c_int(sh_degree), C.c_int(feats.shape[1]),
+        C.c_float(scaling_modifier), C.c_float(sigma_threshold), C.c_int(max_sections), C.c_int(exp_mode), _p(out))
+    return out
+
+
+def transient_batch(scan_o, sin_th, cos_th, sin_ph, cos_ph, t_samples, hscale,
+                    means, log_scales, rots, opac, feats, sh_degree=0, c=1.0, deltaT=0.01,
+                    scaling_modifier=1.0, use_occlusion=False, mode=0, cap=0, exp_mode=1,
+                    precision="f32", count=False):
+    """Batched transient H[S,T]; per-scan-point slice == cuda_autograd.py:254-314 x vp_y^2.
+    Returns H (and counters dict if count)."""
+    scan_o, t_samples, hscale = _f(scan_o).reshape(-1, 3), _f(t_samples), _f(hscale).reshape(-1)
+    S, T = scan_o.shape[0], t_samples.shape[0]
+    sin_th, cos_th, sin_ph, cos_ph = [_f(a).reshape(S, -1) for a in (sin_th, cos_th, sin_ph, cos_ph)]
+    A = sin_th.shape[1]
+    means, log_scales, rots, opac, feats = _f(means), _f(log_scales), _f(rots), _f(opac).reshape(-1), _f(feats)
+    N = means.shape[0]
+    feats = feats.reshape(N, -1)
+    dt, pre = _rt(precision)
+    H = np.zeros((S, T), dt)
+    cnt = np.zeros(4, np.int64) if count else None
+    getattr(lib(), pre + "transient_batch")(
+        _p(scan_o), _p(sin_th), _p(cos_th), _p(sin_ph), _p(cos_ph), _p(t_samples), _p(hscale),
+        _p(means), _p(log_scales), _p(rots), _p(opac), _p(feats),
+        C.c_int(S), C.c_int(A), C.c_int(T), C.c_int(N), C.c_int(sh_degree), C.c_int(feats.shape[1]),
+        C.c_float(c), C.c_float(deltaT), C.c_float(scaling_modifier), C.c_int(int(use_occlusion)),
+        C.c_int(mode), C.c_int(cap), C.c_int(exp_mode), _p(H), _p(cnt))
+    if count:
+        return H, {"hits": int(cnt[0]), "ref_sample_evals": int(cnt[1]), "W_s": int(cnt[2]), "W_b": int(cnt[3])}
+    return H
+
+
+def shell_intervals(scan_o, Sy, Sx, tile_y, tile_x, means, log_scales, scaling_modifier, mcut,
+                    t0, dt, T, bins_per_range, exp_mode=1):
+    scan_o, means, log_scales = _f(scan_o).reshape(-1, 3), _f(means), _f(log_scales)
+    N = means.shape[0]
+    nt = ((Sy + tile_y - 1) // tile_y) * ((Sx + tile_x - 1) // tile_x)
+    lo = np.empty((nt, N), np.int32)
+    hi = np.empty((nt, N), np.int32)
+    lib().orc_shell_intervals(_p(scan_o), C.c_int(Sy), C.c_int(Sx), C.c_int(tile_y), C.c_int(tile_x),
+                              _p(means), _p(log_scales), C.c_int(N), C.c_float(scaling_modifier), C.c_float(mcut),
+                              C.c_int(exp_mode), C.c_float(t0), C.c_float(dt), C.c_int(T), C.c_int(bins_per_range),
+                              _p(lo), _p(hi))
+    return lo, hi
+
+
+def shell_lists(lo, hi, n_ranges):
+    """-> counts [n_tiles*n_ranges], offsets (exclusive scan, int64, len cells+1), list (ascending g per cell)."""
+    lo = np.ascontiguousarray(lo, np.int32)
+    hi = np.ascontiguousarray(hi, np.int32)
+    nt, N = lo.shape
+    counts = np.zeros(nt * n_ranges, np.int32)
+    lib().orc_shell_lists(_p(lo), _p(hi), C.c_int(nt), C.c_int(n_ranges), C.c_int(N), _p(counts), None, None)
+    offsets = np.zeros(nt * n_ranges + 1, np.int64)
+    np.cumsum(counts, out=offsets[1:])
+    lst = np.empty(int(offsets[-1]), np.int32)
+    c2 = np.zeros_like(counts)
+    lib().orc_shell_lists(_p(lo), _p(hi), C.c_int(nt), C.c_int(n_ranges), C.c_int(N), _p(c2), _p(offsets), _p(lst))
+    return counts, offsets, lst
+
+
+def knn_dist2(points):
+    points = _f(points).reshape(-1, 3)
+    out = np.empty(points.shape[0], np.float32)
+    lib().orc_knn_dist2(_p(points), C.c_int(points.shape[0]), _p(out))
+    return out
