@@ -1,0 +1,84 @@
+/* nlosb200.h -- C ABI of libnlosb200.so, the B200 (sm_100a) transient renderer.
+ *
+ * Drop-in boundary for the reference's pybind module `nlos_gaussian_renderer._C`
+ * (/root/reference/submodules/cuda_renderer/src/bindings.cpp:26-35) and for the
+ * torch.autograd.Function that wraps it (gaussian_model/cuda_autograd.py:27-191).
+ *
+ * Conventions: every pointer is a DEVICE pointer to contiguous fp32 / int32 data unless
+ * stated; `stream` is a cudaStream_t passed as void*; calls are stream-ordered and never
+ * synchronise the host; return 0 on success, <0 on error with the message available from
+ * nlosb200_last_error() (thread local).  Inputs are borrowed, outputs are caller-allocated.
+ */
+#ifndef NLOSB200_H
+#define NLOSB200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* nlosb200_last_error(void);
+int nlosb200_version(void);
+int nlosb200_record_floats(void);            /* 32: floats per preprocessed Gaussian record          */
+int nlosb200_grad_floats(void);              /* 16: floats per Gaussian in the packed gradient buffer */
+long long nlosb200_tile_floats(int A);       /* floats per scan tile block for an A x A lattice       */
+int nlosb200_transient_warps_per_block(void);
+int nlosb200_bin_num_chunks(int N);
+
+/* ---- per-Gaussian activation / packing -------------------------------------------------------
+ * Replaces compute_gaussian_bboxes_kernel (include/bbox_compute.cuh:76-120) and the per-sample
+ * re-activation inside volume_render_kernel (src/volume_renderer.cu:86-111).
+ * records [N,32] (128-B aligned), shell [N,4] = (mean, mcut*max scale), bboxes [N,6]; each nullable. */
+int nlosb200_preprocess(const float* means, const float* log_scales, const float* rotations, const float* opacities,
+                        const float* features, int N, int sh_dim, float scaling_modifier, float sigma_bbox, float mcut,
+                        float* records, float* shell, float* bboxes, void* stream);
+/* dacc [N,16] = {dL/dM(9), dL/dmu(3), dL/dop, dL/dalb0, 0, 0} -> raw parameter gradients
+ * (the backward the reference leaves as zeros, gaussian_model/cuda_autograd.py:139-172). */
+int nlosb200_preprocess_backward(const float* log_scales, const float* rotations, const float* opacities, const float* features,
+                                 int N, int sh_dim, float scaling_modifier, const float* dacc, float* d_means,
+                                 float* d_log_scales, float* d_rotations, float* d_opacities, float* d_features, int accumulate,
+                                 void* stream);
+/* GaussianModel.get_bboxes (gaussian_model/gaussian_model.py:140-178) / bbox kernel: [N,6] min xyz, max xyz */
+int nlosb200_compute_bboxes(const float* means, const float* log_scales, const float* rotations, int N, float scaling_modifier,
+                            float sigma, float* bboxes, void* stream);
+
+/* ---- scan tiles: 32 consecutive scan points per tile, lattice of cuda_autograd.py:254-268 ------
+ * scan_o [S,3]; sin_th/cos_th/sin_ph/cos_ph [S,A]; lattice [S,4] = (theta0, dtheta, phi0, dphi) of
+ * the linspace; hscale [S] = dtheta*dphi*vp_y^2 (cuda_autograd.py:311-314, nlos_helpers.py:275-276);
+ * valid int32 [S] nullable (0 = padding lane of a ragged tile);
+ * tiles out: ceil(S/32) * nlosb200_tile_floats(A) floats, 128-B aligned. */
+int nlosb200_build_scan_tiles(const float* scan_o, const float* sin_th, const float* cos_th, const float* sin_ph,
+                              const float* cos_ph, const float* lattice, const float* hscale, const int* valid, int S, int A,
+                              float* tiles, void* stream);
+
+/* ---- shell-intersection binning (replaces filter_gaussians_kernel, src/ray_aabb.cu:10-102, as the
+ * culling structure of the batched renderer).  n_ranges = ceil(T/bins_per_range) <= 64, n_cells = n_tiles*n_ranges.
+ * chunk_counts int32 [n_cells * nlosb200_bin_num_chunks(N)], cell_counts int32 [n_cells],
+ * cell_offsets int64 [n_cells+1], cell_sub_off int32 [n_cells], tile_items int32 [n_tiles+1],
+ * header int64 [4] = {total list entries, CTA work items, overflow flag, -}. */
+int nlosb200_bin_shells_plan(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
+                             int bins_per_range, int slice_len, int warps_per_block, int* chunk_counts, int* cell_counts,
+                             long long* cell_offsets, int* cell_sub_off, int* tile_items, long long* header, void* stream);
+int nlosb200_bin_shells_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
+                             int bins_per_range, const int* chunk_counts_scanned, const long long* cell_offsets, int* list,
+                             long long list_capacity, long long* header, void* stream);
+
+/* ---- batched transient H[n_tiles*32, T] and its backward.  mode 0 = numerical (volume_renderer.cu
+ * no-occlusion branch :139-182), 1 = analytic-exact per-bin integral.
+ * bin k sits at radius t0 + k*dt.  H and dacc are zeroed by the callee. */
+int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                               const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items,
+                               int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float c_deltaT,
+                               float mcut, int mode, float* H, void* stream);
+int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                                const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items,
+                                int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float c_deltaT,
+                                float mcut, int mode, const float* grad_H, float* dacc, void* stream);
+/* counters uint64 [4]: hit (g,ray) pairs, W_s, sample-evals evaluated, W_b */
+int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                             const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items,
+                             int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float mcut,
+                             unsigned long long* counters, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,243 @@
+// common.cuh -- shared device helpers for libnlosb200 (sm_100a only).
+//
+// Conventions
+//   * "record": the 32-float (128 B, 128 B aligned) per-Gaussian block written by
+//     the preprocess kernel and gathered into shared memory with TMA bulk copies.
+//   * functions suffixed _x ("exact") use only correctly-rounded single IEEE
+//     operations (__fadd_rn/__fmul_rn/__fmaf_rn/__fsqrt_rn/__frcp_rn) in a fixed
+//     order, so that culling decisions are bit-identical to the CPU oracle
+//     (oracle/nlos_oracle.c, compiled with -ffp-contract=off).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define NLOS_REC_FLOATS 32
+#define NLOS_GRAD_FLOATS 16
+#define NLOS_TILE 32          // scan points per tile == lanes per warp
+#define NLOS_NTAB 7           // per-tile lattice tables
+#define NLOS_PINFO_ROWS 12
+
+// record layout (float index)
+#define REC_MU 0      // 0..2 mean
+#define REC_OP 3      // sigmoid(opacity logit)
+#define REC_M 4       // 4..12  M = diag(1/(s+1e-8)) R^T, row major  (m2 = |M (x-mu)|^2)
+#define REC_BMIN 13   // 13..15 3-sigma AABB min  (bbox_compute.cuh:23-120)
+#define REC_BMAX 16   // 16..18 3-sigma AABB max
+#define REC_ALB 19    // degree-0 albedo  max(C0*f0 + 0.5, 0)
+#define REC_RAD 20    // mcut * max(scale)
+#define REC_S 21      // 21..23 activated scales
+
+// lattice tables per tile: [NLOS_NTAB][A][32]
+#define TAB_STH 0
+#define TAB_CTH 1
+#define TAB_TTH 2     // sin/cos (theta)
+#define TAB_SPH 3
+#define TAB_CPH 4
+#define TAB_ISPH 5    // 1/sin(phi)
+#define TAB_ICPH 6    // 1/cos(phi)
+// pinfo rows: [NLOS_PINFO_ROWS][32]
+#define PI_OX 0
+#define PI_OY 1
+#define PI_OZ 2
+#define PI_TH0 3
+#define PI_IDTH 4
+#define PI_PH0 5
+#define PI_IDPH 6
+#define PI_HSCALE 7
+#define PI_FLAGS 8    // bit0 valid, bit1 fast footprint ok
+
+#define NLOS_SH_C0 0.28209479177387814f
+
+namespace nlos {
+
+// ---------------------------------------------------------------- exact math
+// det_expf: identical operation sequence to oracle/nlos_oracle.c:det_expf
+__device__ __forceinline__ float det_expf(float x)
+{
+    if (x > 88.0f) x = 88.0f;
+    if (x < -87.0f) x = -87.0f;
+    float t = __fmul_rn(x, 1.4426950408889634f);
+    float n = rintf(t);
+    float r = __fmaf_rn(n, -0.693145751953125f, x);
+    r = __fmaf_rn(n, -1.42860682030941723212e-6f, r);
+    float p = 1.9875691500e-4f;
+    p = __fmaf_rn(p, r, 1.3981999507e-3f);
+    p = __fmaf_rn(p, r, 8.3334519073e-3f);
+    p = __fmaf_rn(p, r, 4.1665795894e-2f);
+    p = __fmaf_rn(p, r, 1.6666665459e-1f);
+    p = __fmaf_rn(p, r, 5.0000001201e-1f);
+    p = __fmaf_rn(p, __fmul_rn(r, r), r);
+    p = __fadd_rn(p, 1.0f);
+    int e = (int)n;
+    float s = __int_as_float((e + 127) << 23);
+    return __fmul_rn(p, s);
+}
+
+// cuda_utils.cuh:54-85 quat_to_rotmat (w,x,y,z; normalised inside; identity if |q|<1e-8),
+// evaluated with the oracle's operation order.  Returns false for the identity fallback.
+__device__ __forceinline__ bool quat_to_rotmat_x(float w, float x, float y, float z, float* R, float* inv_norm_out = nullptr)
+{
+    float n2 = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(w, w), __fmul_rn(x, x)), __fmul_rn(y, y)), __fmul_rn(z, z));
+    float norm = __fsqrt_rn(n2);
+    if (norm < 1e-8f) {
+        R[0] = 1; R[1] = 0; R[2] = 0; R[3] = 0; R[4] = 1; R[5] = 0; R[6] = 0; R[7] = 0; R[8] = 1;
+        if (inv_norm_out) *inv_norm_out = 0.f;
+        return false;
+    }
+    w = __fdiv_rn(w, norm); x = __fdiv_rn(x, norm); y = __fdiv_rn(y, norm); z = __fdiv_rn(z, norm);
+    if (inv_norm_out) *inv_norm_out = __frcp_rn(norm);
+    R[0] = __fsub_rn(1.0f, __fmul_rn(2.0f, __fadd_rn(__fmul_rn(y, y), __fmul_rn(z, z))));
+    R[1] = __fmul_rn(2.0f, __fsub_rn(__fmul_rn(x, y), __fmul_rn(w, z)));
+    R[2] = __fmul_rn(2.0f, __fadd_rn(__fmul_rn(x, z), __fmul_rn(w, y)));
+    R[3] = __fmul_rn(2.0f, __fadd_rn(__fmul_rn(x, y), __fmul_rn(w, z)));
+    R[4] = __fsub_rn(1.0f, __fmul_rn(2.0f, __fadd_rn(__fmul_rn(x, x), __fmul_rn(z, z))));
+    R[5] = __fmul_rn(2.0f, __fsub_rn(__fmul_rn(y, z), __fmul_rn(w, x)));
+    R[6] = __fmul_rn(2.0f, __fsub_rn(__fmul_rn(x, z), __fmul_rn(w, y)));
+    R[7] = __fmul_rn(2.0f, __fadd_rn(__fmul_rn(y, z), __fmul_rn(w, x)));
+    R[8] = __fsub_rn(1.0f, __fmul_rn(2.0f, __fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y))));
+    return true;
+}
+
+// 3-sigma extent of one axis: sigma * sqrt((Ra sx)^2 + (Rb sy)^2 + (Rc sz)^2)   (bbox_compute.cuh:23-74)
+__device__ __forceinline__ float extent_x(float ra, float rb, float rc, float sx, float sy, float sz, float sigma)
+{
+    float a = __fmul_rn(ra, sx), b = __fmul_rn(rb, sy), c = __fmul_rn(rc, sz);
+    float s = __fadd_rn(__fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b)), __fmul_rn(c, c));
+    return __fmul_rn(sigma, __fsqrt_rn(s));
+}
+
+// cuda_utils.cuh:97-121 ray_aabb_intersect, bit-exact: inv = 1/(d + 1e-8) per axis
+__device__ __forceinline__ bool ray_aabb_x(float ox, float oy, float oz, float dx, float dy, float dz,
+                                           const float* __restrict__ b, float* tmin_o = nullptr, float* tmax_o = nullptr)
+{
+    float ix = __frcp_rn(__fadd_rn(dx, 1e-8f)), iy = __frcp_rn(__fadd_rn(dy, 1e-8f)), iz = __frcp_rn(__fadd_rn(dz, 1e-8f));
+    float t0x = __fmul_rn(__fsub_rn(b[0], ox), ix), t0y = __fmul_rn(__fsub_rn(b[1], oy), iy), t0z = __fmul_rn(__fsub_rn(b[2], oz), iz);
+    float t1x = __fmul_rn(__fsub_rn(b[3], ox), ix), t1y = __fmul_rn(__fsub_rn(b[4], oy), iy), t1z = __fmul_rn(__fsub_rn(b[5], oz), iz);
+    float tmin = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
+    float tmax = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+    if (tmin_o) *tmin_o = tmin;
+    if (tmax_o) *tmax_o = tmax;
+    return tmax >= tmin && tmax >= 0.0f;
+}
+
+// ---------------------------------------------------------------- fast math (SFU aware)
+__device__ __forceinline__ float ex2_approx(float x)
+{
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rcp_approx(float x)
+{
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float sqrt_approx(float x)
+{
+    float y;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+// atan2 with |error| < 2e-6 rad (one MUFU.RCP + 6 FMA); used only for conservative
+// footprint rectangles, which are widened by a far larger margin.
+__device__ __forceinline__ float atan2_fast(float y, float x)
+{
+    float ax = fabsf(x), ay = fabsf(y);
+    float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+    float a = mn * rcp_approx(fmaxf(mx, 1e-30f));
+    float s = a * a;
+    float p = -0.01172120f;
+    p = fmaf(p, s, 0.05265332f);
+    p = fmaf(p, s, -0.11643287f);
+    p = fmaf(p, s, 0.19354346f);
+    p = fmaf(p, s, -0.33262347f);
+    p = fmaf(p, s, 0.99997726f);
+    float r = p * a;
+    if (ay > ax) r = 1.57079632679f - r;
+    if (x < 0.f) r = 3.14159265359f - r;
+    return y < 0.f ? -r : r;
+}
+
+// erf with |abs error| <= ~1.2e-7 : odd polynomial for |x|<1 , 1-exp(poly) beyond (CUDA-libm style split)
+__device__ __forceinline__ float erf_fast(float x)
+{
+    return erff(x);
+}
+
+__device__ __forceinline__ float warp_sum(float v)
+{
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    return v;
+}
+
+// ---------------------------------------------------------------- TMA bulk copy + mbarrier (PTX)
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    uint32_t addr = smem_u32(bar);
+    uint32_t ok = 0;
+    while (!ok) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(addr), "r"(parity)
+            : "memory");
+    }
+}
+// 1-D TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+}  // namespace nlos
+
+// ---------------------------------------------------------------- host-side error plumbing
+#include <stdio.h>
+#include <string.h>
+namespace nlos {
+void set_error(const char* fmt, ...);
+}
+#define NLOS_CHECK_LAUNCH(name)                                                   \
+    do {                                                                          \
+        cudaError_t e__ = cudaGetLastError();                                     \
+        if (e__ != cudaSuccess) {                                                 \
+            nlos::set_error("%s: %s", name, cudaGetErrorString(e__));             \
+            return -2;                                                            \
+        }                                                                         \
+    } while (0)
+#define NLOS_REQUIRE(cond, ...)                                                   \
+    do {                                                                          \
+        if (!(cond)) {                                                            \
+            nlos::set_error(__VA_ARGS__);                                         \
+            return -1;                                                            \
+        }                                                                         \
+    } while (0)

@@ -1,0 +1,510 @@
+// transient.cu -- batched confocal transient renderer  H[scan point, time bin]  and its backward pass.
+//
+// One launch renders a whole slab of the relay-wall grid.  Per scan point the result equals what the
+// reference produces with one CUDARenderModule.forward call per optimiser step
+// (/root/reference/gaussian_model/cuda_autograd.py:254-314 -> submodules/cuda_renderer/src/volume_renderer.cu:16-185,
+// no-occlusion branch :139-182) times volume_position[1]^2 (nlos_helpers.py:275-276), without the
+// 256-Gaussians-per-ray cap (ray_aabb.cu:6,39).  The backward pass is what cuda_autograd.py:139-172 leaves as zeros.
+//
+// Work decomposition (B200: 148 SMs, 2 CTAs of 8 warps per SM):
+//   CTA  = one scan tile (32 scan points) ; its lattice tables arrive with ONE TMA bulk copy
+//   warp = one (time-bin range, list slice) of that tile ; lane = scan point
+//   each warp owns a private [bins_per_range][32] shared-memory accumulator (bank == lane -> conflict free
+//   read-modify-write without atomics), gathers Gaussian records with per-record TMA bulk copies through a
+//   2-stage mbarrier ring, and flushes once per slice with coalesced float REDs.
+//   Per (Gaussian, scan point): conservative (theta,phi) footprint rectangle from the 3-sigma AABB, exact
+//   slab test per candidate ray (same predicate as cuda_utils.cuh:97-121), per hit ray the quadratic
+//   m2(r) = m2min + C (r - r*)^2 in centred form, then 1 MUFU.EX2 + 4 FP32 ops per (Gaussian, ray, bin).
+//   Backward: per ray three weighted moments of exp(-m2/2) in registers, chain rule to dL/dM, dL/dmu,
+//   dL/dop, dL/dalb per lane, ONE warp-shuffle reduction per (Gaussian, slice), 13 float REDs.
+#include "common.cuh"
+#include "../../include/nlosb200.h"
+
+using namespace nlos;
+
+#define TR_WPB 8           // warps per CTA
+#define TR_RING 4          // records per ring stage
+#define TR_STAGES 2
+#define LOG2E_F 1.4426950408889634f
+#define TWO_OVER_SQRT_PI 1.1283791670955126f
+
+enum { MODE_NUM = 0, MODE_ANA = 1, MODE_COUNT = 2 };
+
+struct TransientParams {
+    const float* tiles;
+    int n_tiles, A;
+    const float* records;
+    int N;
+    const int* list;
+    const long long* cell_offsets;
+    const int* cell_counts;
+    const int* cell_sub_off;
+    const int* tile_items;
+    float t0, dt, inv_dt;
+    int T, bpr, n_ranges, slice_len;
+    float flush_scale;   // c*deltaT for the numerical mode (volume_renderer.cu:182), 1 for the analytic-exact mode
+    float mcut2;
+    float* H;            // forward out   [n_tiles*32, T]  (accumulated with REDs; caller zeroes)
+    const float* gH;     // backward in   [n_tiles*32, T]
+    float* dacc;         // backward out  [N, 16]          (accumulated with REDs; caller zeroes)
+    unsigned long long* counters;   // MODE_COUNT: [0] hit (g,ray) pairs, [1] W_s, [2] evaluated sample-evals, [3] W_b
+};
+
+__device__ __forceinline__ int clamp_ceil(float x, int lo, int hi)
+{
+    x = ceilf(x);
+    return x <= (float)lo ? lo : (x >= (float)hi ? hi : (int)x);
+}
+__device__ __forceinline__ int clamp_floor(float x, int lo, int hi)
+{
+    x = floorf(x);
+    return x <= (float)lo ? lo : (x >= (float)hi ? hi : (int)x);
+}
+
+template <int MODE, bool BWD>
+__global__ void __launch_bounds__(TR_WPB * 32, 2) transient_kernel(const TransientParams P)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int A = P.A;
+    const int tile_floats = (NLOS_NTAB * A + NLOS_PINFO_ROWS) * NLOS_TILE;
+    float* s_tab = reinterpret_cast<float*>(smem_raw);
+    float* s_pi = s_tab + NLOS_NTAB * A * NLOS_TILE;
+    float* s_H = s_tab + tile_floats;                                   // [TR_WPB][bpr][32]
+    float* s_ring = s_H + TR_WPB * P.bpr * NLOS_TILE;                   // [TR_WPB][TR_STAGES][TR_RING][32]
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_ring + TR_WPB * TR_STAGES * TR_RING * NLOS_REC_FLOATS);   // [1 + TR_WPB*TR_STAGES]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int item = blockIdx.x;
+    const int n_items = P.tile_items[P.n_tiles];
+    if (item >= n_items) return;
+
+    // tile of this CTA item: largest t with tile_items[t] <= item
+    int tile;
+    {
+        int lo = 0, hi = P.n_tiles - 1;
+        while (lo < hi) {
+            int mid = (lo + hi + 1) >> 1;
+            if (P.tile_items[mid] <= item) lo = mid; else hi = mid - 1;
+        }
+        tile = lo;
+    }
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar[0], 1);
+        for (int i = 0; i < TR_WPB * TR_STAGES; ++i) mbar_init(&s_bar[1 + i], 1);
+        mbar_fence_init();
+        mbar_arrive_expect_tx(&s_bar[0], (uint32_t)tile_floats * 4u);
+        bulk_g2s(s_tab, P.tiles + (size_t)tile * tile_floats, (uint32_t)tile_floats * 4u, &s_bar[0]);
+    }
+    __syncthreads();
+
+    // ---- which (range, slice) does this warp own?
+    const int sub = (item - P.tile_items[tile]) * TR_WPB + warp;
+    const int* sub_off = P.cell_sub_off + (size_t)tile * P.n_ranges;
+    const int* ccnt = P.cell_counts + (size_t)tile * P.n_ranges;
+    int r = -1;
+    {
+        int r0 = lane, r1 = lane + 32;
+        bool m0 = r0 < P.n_ranges && sub_off[r0] <= sub && ccnt[r0] > 0;
+        bool m1 = r1 < P.n_ranges && sub_off[r1] <= sub && ccnt[r1] > 0;
+        unsigned b0 = __ballot_sync(0xffffffffu, m0), b1 = __ballot_sync(0xffffffffu, m1);
+        if (b1) r = 63 - __clz(b1); else if (b0) r = 31 - __clz(b0);
+    }
+    long long beg = 0;
+    int n = 0;
+    if (r >= 0) {
+        int slice = sub - sub_off[r];
+        int cnt = ccnt[r];
+        int first = slice * P.slice_len;
+        if (first < cnt) {
+            n = min(P.slice_len, cnt - first);
+            beg = P.cell_offsets[(size_t)tile * P.n_ranges + r] + first;
+        }
+    }
+    mbar_wait(&s_bar[0], 0);   // lattice tables + scan-point info have landed
+    if (n == 0) return;
+
+    const int Rlo = r * P.bpr, Rhi = min(Rlo + P.bpr, P.T) - 1;
+    const int nb = Rhi - Rlo + 1;
+    float* Hw = s_H + warp * P.bpr * NLOS_TILE;
+    float* ring = s_ring + warp * TR_STAGES * TR_RING * NLOS_REC_FLOATS;
+    uint64_t* bar = s_bar + 1 + warp * TR_STAGES;
+
+    // ---- per-lane scan point
+    const float ox = s_pi[PI_OX * 32 + lane], oy = s_pi[PI_OY * 32 + lane], oz = s_pi[PI_OZ * 32 + lane];
+    const float th0 = s_pi[PI_TH0 * 32 + lane], idth = s_pi[PI_IDTH * 32 + lane];
+    const float ph0 = s_pi[PI_PH0 * 32 + lane], idph = s_pi[PI_IDPH * 32 + lane];
+    const int flags = __float_as_int(s_pi[PI_FLAGS * 32 + lane]);
+    const bool valid = flags & 1, fast = flags & 2;
+    const float t0 = P.t0, dt = P.dt, inv_dt = P.inv_dt;
+    // radial extent of this warp's bins (bin k covers [t0+(k-.5)dt, t0+(k+.5)dt])
+    const float r_in = fmaf((float)Rlo - 0.5f, dt, t0), r_out = fmaf((float)Rhi + 0.5f, dt, t0);
+
+    if (MODE != MODE_COUNT) {
+        if (!BWD) {
+            for (int i = lane; i < nb * NLOS_TILE; i += 32) Hw[i] = 0.f;
+        } else {
+            // weights  W[k][p] = dL/dH[p,k] * hscale_p / (r_k^2 + 1e-8) * flush_scale     (cuda_autograd.py:308)
+            for (int pp = 0; pp < NLOS_TILE; ++pp) {
+                float hs = s_pi[PI_HSCALE * 32 + pp] * P.flush_scale;
+                const float* gsrc = P.gH + ((size_t)tile * NLOS_TILE + pp) * P.T + Rlo;
+                for (int kl = lane; kl < nb; kl += 32) {
+                    float rk = fmaf((float)(Rlo + kl), dt, t0);
+                    Hw[kl * NLOS_TILE + pp] = gsrc[kl] * hs / (rk * rk + 1e-8f);
+                }
+            }
+        }
+        __syncwarp();
+    }
+    unsigned long long c_hits = 0, c_ws = 0, c_ev = 0, c_wb = 0;
+
+    // ---- TMA ring over the list slice
+    const int n_batches = (n + TR_RING - 1) / TR_RING;
+    int gid_next = 0, gid_cur = 0;
+    auto issue = [&](int b) {
+        int stage = b & 1;
+        int cnt = min(TR_RING, n - b * TR_RING);
+        if (lane == 0) mbar_arrive_expect_tx(&bar[stage], (uint32_t)cnt * NLOS_REC_FLOATS * 4u);
+        __syncwarp();
+        gid_next = 0;
+        if (lane < cnt) {
+            gid_next = P.list[beg + b * TR_RING + lane];
+            bulk_g2s(ring + (stage * TR_RING + lane) * NLOS_REC_FLOATS, P.records + (size_t)gid_next * NLOS_REC_FLOATS,
+                     NLOS_REC_FLOATS * 4u, &bar[stage]);
+        }
+    };
+    issue(0);
+    for (int b = 0; b < n_batches; ++b) {
+        gid_cur = gid_next;
+        if (b + 1 < n_batches) issue(b + 1);   // (overwrites gid_next; gid_cur keeps this batch's ids)
+        mbar_wait(&bar[b & 1], (b >> 1) & 1);
+        const int cnt = min(TR_RING, n - b * TR_RING);
+        for (int q = 0; q < cnt; ++q) {
+            const float4* rec = reinterpret_cast<const float4*>(ring + ((b & 1) * TR_RING + q) * NLOS_REC_FLOATS);
+            const float4 v0 = rec[0], v1 = rec[1], v2 = rec[2], v3 = rec[3], v4 = rec[4], v5 = rec[5];
+            const float M00 = v1.x, M01 = v1.y, M02 = v1.z, M10 = v1.w, M11 = v2.x, M12 = v2.y, M20 = v2.z, M21 = v2.w, M22 = v3.x;
+            const float opalb = v0.w * v4.w;
+            // accumulators of the backward pass for this (Gaussian, scan point)
+            float gax = 0.f, gay = 0.f, gaz = 0.f;                                                  // dL/da
+            float g00 = 0.f, g01 = 0.f, g02 = 0.f, g10 = 0.f, g11 = 0.f, g12 = 0.f, g20 = 0.f, g21 = 0.f, g22 = 0.f;   // sum dL/db (x) d
+            float gwa = 0.f;                                                                        // dL/d(op*alb)
+            const float cx = v0.x - ox, cy = v0.y - oy, cz = v0.z - oz;                             // mu - o
+            bool act = valid;
+            if (act) {
+                // radial reject of this scan point against the warp's bins
+                float D = sqrtf(cx * cx + cy * cy + cz * cz);
+                act = (D + v5.x >= r_in) && (D - v5.x <= r_out);
+            }
+            if (act) {
+                const float lox = v3.y - ox, loy = v3.z - oy, loz = v3.w - oz;                      // AABB relative to the scan point
+                const float hix = v4.x - ox, hiy = v4.y - oy, hiz = v4.z - oz;
+                const float ax = -(M00 * cx + M01 * cy + M02 * cz), ay = -(M10 * cx + M11 * cy + M12 * cz),
+                            az = -(M20 * cx + M21 * cy + M22 * cz);                                 // a = M (o - mu)
+                // ---- conservative footprint rectangle in lattice index space
+                int i0 = 0, i1 = A - 1, j0 = 0, j1 = A - 1;
+                if (fast) {
+                    float qx = fmaxf(fmaxf(lox, -hix), 0.f), qy = fmaxf(fmaxf(loy, -hiy), 0.f);
+                    float rmin = sqrtf(qx * qx + qy * qy);
+                    float bx = fmaxf(fabsf(lox), fabsf(hix)), by = fmaxf(fabsf(loy), fabsf(hiy));
+                    float rmax = sqrtf(bx * bx + by * by);
+                    float thlo = atan2_fast(hiz > 0.f ? rmin : rmax, hiz);
+                    float thhi = atan2_fast(loz > 0.f ? rmax : rmin, loz);
+                    i0 = clamp_ceil((thlo - th0) * idth - 0.02f, 0, A);
+                    i1 = clamp_floor((thhi - th0) * idth + 0.02f, -1, A - 1);
+                    if (loy > 0.f) {
+                        float phhi = atan2_fast(lox > 0.f ? hiy : loy, lox);
+                        float phlo = atan2_fast(hix > 0.f ? loy : hiy, hix);
+                        j0 = clamp_ceil((phlo - ph0) * idph - 0.02f, 0, A);
+                        j1 = clamp_floor((phhi - ph0) * idph + 0.02f, -1, A - 1);
+                    }
+                }
+                int wb_lo = 0x7fffffff, wb_hi = -1;
+                for (int i = i0; i <= i1; ++i) {
+                    const float sth = s_tab[(TAB_STH * A + i) * 32 + lane], cth = s_tab[(TAB_CTH * A + i) * 32 + lane];
+                    const float tth = s_tab[(TAB_TTH * A + i) * 32 + lane];
+                    const float tz0 = loz * tth, tz1 = hiz * tth;
+                    const float zmn = fminf(tz0, tz1), zmx = fmaxf(tz0, tz1);
+                    for (int j = j0; j <= j1; ++j) {
+                        // slab test of cuda_utils.cuh:97-121 with every t multiplied by sin(theta) > 0
+                        const float icp = s_tab[(TAB_ICPH * A + j) * 32 + lane], isp = s_tab[(TAB_ISPH * A + j) * 32 + lane];
+                        const float tx0 = lox * icp, tx1 = hix * icp, ty0 = loy * isp, ty1 = hiy * isp;
+                        const float tmin = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), zmn);
+                        const float tmax = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), zmx);
+                        if (!(tmax >= tmin && tmax >= 0.f)) continue;
+                        const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
+                        const float dx = sth * cph, dy = sth * sph, dz = cth;
+                        const float bx = M00 * dx + M01 * dy + M02 * dz, by = M10 * dx + M11 * dy + M12 * dz,
+                                    bz = M20 * dx + M21 * dy + M22 * dz;                            // b = M d
+                        const float C = bx * bx + by * by + bz * bz;
+                        const float ab = ax * bx + ay * by + az * bz;
+                        const float rs = -ab / C;                                                   // closest approach r*
+                        const float px = fmaf(rs, bx, ax), py = fmaf(rs, by, ay), pz = fmaf(rs, bz, az);
+                        const float m2min = px * px + py * py + pz * pz;
+                        const float h2 = (P.mcut2 - m2min) / C;
+                        if (MODE == MODE_COUNT) {
+                            // slab interval stretched about its midpoint by 5.3/3 (t = t'/sin(theta))
+                            float ist = 1.0f / sth;
+                            float mid = 0.5f * (tmin + tmax) * ist, half = 0.5f * (tmax - tmin) * ist * (5.3f / 3.0f);
+                            int ka = clamp_ceil((mid - half - t0) * inv_dt, Rlo, Rhi + 1), kb = clamp_floor((mid + half - t0) * inv_dt, Rlo - 1, Rhi);
+                            c_hits += (r_in <= mid && mid < r_out) ? 1 : 0;
+                            if (kb >= ka) { c_ws += kb - ka + 1; wb_lo = min(wb_lo, ka); wb_hi = max(wb_hi, kb); }
+                        }
+                        if (!(h2 > 0.f)) continue;
+                        const float h = sqrtf(h2);
+                        int klo, khi;
+                        if (MODE == MODE_ANA) {
+                            klo = clamp_ceil((rs - h - t0) * inv_dt - 0.5f, Rlo, Rhi + 1);
+                            khi = clamp_floor((rs + h - t0) * inv_dt + 0.5f, Rlo - 1, Rhi);
+                        } else {
+                            klo = clamp_ceil((rs - h - t0) * inv_dt, Rlo, Rhi + 1);
+                            khi = clamp_floor((rs + h - t0) * inv_dt, Rlo - 1, Rhi);
+                        }
+                        if (klo > khi) continue;
+                        float* hp = Hw + (klo - Rlo) * NLOS_TILE + lane;
+                        const float wt = opalb * sth;
+                        if (MODE == MODE_COUNT) {
+                            c_ev += khi - klo + 1;
+                        } else if (MODE == MODE_NUM) {
+                            const float gam = -0.5f * LOG2E_F * C, al = -0.5f * LOG2E_F * m2min;
+                            float t = fmaf((float)klo, dt, t0) - rs;
+                            if (!BWD) {
+#pragma unroll 4
+                                for (int k = klo; k <= khi; ++k) {
+                                    float e = ex2_approx(fmaf(gam, t * t, al));
+                                    *hp = fmaf(wt, e, *hp);
+                                    hp += NLOS_TILE;
+                                    t += dt;
+                                }
+                            } else {
+                                float S0 = 0.f, S1 = 0.f, S2 = 0.f;
+#pragma unroll 4
+                                for (int k = klo; k <= khi; ++k) {
+                                    float we = *hp * ex2_approx(fmaf(gam, t * t, al));
+                                    float wet = we * t;
+                                    S0 += we;
+                                    S1 += wet;
+                                    S2 = fmaf(wet, t, S2);
+                                    hp += NLOS_TILE;
+                                    t += dt;
+                                }
+                                gwa = fmaf(sth, S0, gwa);
+                                // dL/da = -wt (S0 perp + S1 b) ; dL/db = -wt (r* (S0 perp + S1 b) + S1 perp + S2 b)
+                                const float ux = S0 * px + S1 * bx, uy = S0 * py + S1 * by, uz = S0 * pz + S1 * bz;
+                                const float vx = fmaf(rs, ux, S1 * px + S2 * bx), vy = fmaf(rs, uy, S1 * py + S2 * by),
+                                            vz = fmaf(rs, uz, S1 * pz + S2 * bz);
+                                gax = fmaf(-wt, ux, gax); gay = fmaf(-wt, uy, gay); gaz = fmaf(-wt, uz, gaz);
+                                const float bxw = -wt * vx, byw = -wt * vy, bzw = -wt * vz;
+                                g00 = fmaf(bxw, dx, g00); g01 = fmaf(bxw, dy, g01); g02 = fmaf(bxw, dz, g02);
+                                g10 = fmaf(byw, dx, g10); g11 = fmaf(byw, dy, g11); g12 = fmaf(byw, dz, g12);
+                                g20 = fmaf(bzw, dx, g20); g21 = fmaf(bzw, dy, g21); g22 = fmaf(bzw, dz, g22);
+                            }
+                        } else {   // MODE_ANA : exact bin integrals, erf shared between adjacent bin edges
+                            const float sq = sqrtf(0.5f * C);
+                            const float pref = sqrtf(1.5707963267948966f / C) * ex2_approx(-0.5f * LOG2E_F * m2min);
+                            float u = fmaf((float)klo - 0.5f, dt, t0) - rs;   // lower edge of bin klo, relative to r*
+                            float z = sq * u;
+                            const float dz_ = sq * dt;
+                            float Ep = erf_fast(z);
+                            if (!BWD) {
+                                const float wa = wt * pref;
+#pragma unroll 2
+                                for (int k = klo; k <= khi; ++k) {
+                                    z += dz_;
+                                    float E = erf_fast(z);
+                                    *hp = fmaf(wa, E - Ep, *hp);
+                                    Ep = E;
+                                    hp += NLOS_TILE;
+                                }
+                            } else {
+                                float F = 0.f, P1 = 0.f, P2 = 0.f;
+                                float Dp = TWO_OVER_SQRT_PI * ex2_approx(-LOG2E_F * z * z);
+                                float DUp = Dp * u;
+#pragma unroll 2
+                                for (int k = klo; k <= khi; ++k) {
+                                    z += dz_;
+                                    u += dt;
+                                    float E = erf_fast(z);
+                                    float Dn = TWO_OVER_SQRT_PI * ex2_approx(-LOG2E_F * z * z);
+                                    float DUn = Dn * u;
+                                    float w = *hp;
+                                    F = fmaf(w, E - Ep, F);
+                                    P1 = fmaf(w, Dn - Dp, P1);
+                                    P2 = fmaf(w, DUn - DUp, P2);
+                                    Ep = E; Dp = Dn; DUp = DUn;
+                                    hp += NLOS_TILE;
+                                }
+                                gwa = fmaf(sth * pref, F, gwa);
+                                const float iC = 1.0f / C;
+                                const float gpref = wt * F, gsq = wt * pref * P2, grs = -wt * pref * sq * P1;
+                                const float gm = -0.5f * gpref * pref;
+                                const float k1 = grs * iC;                                  // multiplies (perp + r* b) and b
+                                const float k2 = gsq / (2.0f * sq) - gpref * pref * iC;     // multiplies b
+                                // dL/da = 2 gm perp - k1 b ;  dL/db = 2 gm r* perp - k1 (perp + r* b) + k2 b
+                                const float dax = 2.f * gm * px - k1 * bx, day = 2.f * gm * py - k1 * by, daz = 2.f * gm * pz - k1 * bz;
+                                const float dbx = 2.f * gm * rs * px - k1 * fmaf(rs, bx, px) + k2 * bx;
+                                const float dby = 2.f * gm * rs * py - k1 * fmaf(rs, by, py) + k2 * by;
+                                const float dbz = 2.f * gm * rs * pz - k1 * fmaf(rs, bz, pz) + k2 * bz;
+                                gax += dax; gay += day; gaz += daz;
+                                g00 = fmaf(dbx, dx, g00); g01 = fmaf(dbx, dy, g01); g02 = fmaf(dbx, dz, g02);
+                                g10 = fmaf(dby, dx, g10); g11 = fmaf(dby, dy, g11); g12 = fmaf(dby, dz, g12);
+                                g20 = fmaf(dbz, dx, g20); g21 = fmaf(dbz, dy, g21); g22 = fmaf(dbz, dz, g22);
+                            }
+                        }
+                    }
+                }
+                if (MODE == MODE_COUNT && wb_hi >= wb_lo) c_wb += wb_hi - wb_lo + 1;
+            }
+            if (BWD && MODE != MODE_COUNT) {
+                // a = M (o - mu) = -M c :  dL/dM += dL/da (x) (o - mu) ;  dL/dmu = -M^T dL/da
+                float o[13];
+                o[0] = fmaf(-gax, cx, g00); o[1] = fmaf(-gax, cy, g01); o[2] = fmaf(-gax, cz, g02);
+                o[3] = fmaf(-gay, cx, g10); o[4] = fmaf(-gay, cy, g11); o[5] = fmaf(-gay, cz, g12);
+                o[6] = fmaf(-gaz, cx, g20); o[7] = fmaf(-gaz, cy, g21); o[8] = fmaf(-gaz, cz, g22);
+                o[9] = -(M00 * gax + M10 * gay + M20 * gaz);
+                o[10] = -(M01 * gax + M11 * gay + M21 * gaz);
+                o[11] = -(M02 * gax + M12 * gay + M22 * gaz);
+                o[12] = gwa;
+#pragma unroll
+                for (int i = 0; i < 13; ++i) o[i] = warp_sum(o[i]);
+                const int g = __shfl_sync(0xffffffffu, gid_cur, q);
+                if (lane < 14) {
+                    // slots: 0..8 dM, 9..11 dmu, 12 dop = alb * d(op*alb), 13 dalb = op * d(op*alb)
+                    float val = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 12; ++i) val = (lane == i) ? o[i] : val;
+                    if (lane == 12) val = o[12] * v4.w;
+                    if (lane == 13) val = o[12] * v0.w;
+                    if (val != 0.f) atomicAdd(P.dacc + (size_t)g * NLOS_GRAD_FLOATS + lane, val);
+                }
+            }
+        }
+        __syncwarp();
+    }
+
+    if (MODE == MODE_COUNT) {
+        for (int o = 16; o > 0; o >>= 1) {
+            c_hits += __shfl_xor_sync(0xffffffffu, c_hits, o);
+            c_ws += __shfl_xor_sync(0xffffffffu, c_ws, o);
+            c_ev += __shfl_xor_sync(0xffffffffu, c_ev, o);
+            c_wb += __shfl_xor_sync(0xffffffffu, c_wb, o);
+        }
+        if (lane == 0) {
+            atomicAdd(P.counters + 0, c_hits);
+            atomicAdd(P.counters + 1, c_ws);
+            atomicAdd(P.counters + 2, c_ev);
+            atomicAdd(P.counters + 3, c_wb);
+        }
+        return;
+    }
+    if (!BWD) {
+        // ---- flush: H[p,k] += acc * hscale_p / (r_k^2 + 1e-8) * flush_scale     (cuda_autograd.py:308-314)
+        __syncwarp();
+        for (int pp = 0; pp < NLOS_TILE; ++pp) {
+            float hs = s_pi[PI_HSCALE * 32 + pp] * P.flush_scale;
+            if (hs == 0.f) continue;
+            float* dst = P.H + ((size_t)tile * NLOS_TILE + pp) * P.T + Rlo;
+            for (int kl = lane; kl < nb; kl += 32) {
+                float v = Hw[kl * NLOS_TILE + pp];
+                if (v != 0.f) {
+                    float rk = fmaf((float)(Rlo + kl), dt, t0);
+                    atomicAdd(dst + kl, v * hs / (rk * rk + 1e-8f));
+                }
+            }
+        }
+    }
+}
+
+static size_t transient_smem_bytes(int A, int bpr)
+{
+    size_t f = (size_t)(NLOS_NTAB * A + NLOS_PINFO_ROWS) * NLOS_TILE + (size_t)TR_WPB * bpr * NLOS_TILE +
+               (size_t)TR_WPB * TR_STAGES * TR_RING * NLOS_REC_FLOATS;
+    return f * 4 + (1 + TR_WPB * TR_STAGES) * 8 + 16;
+}
+
+template <int MODE, bool BWD>
+static int launch_transient(const TransientParams& P, int n_cta_items, cudaStream_t s, const char* name)
+{
+    size_t smem = transient_smem_bytes(P.A, P.bpr);
+    NLOS_REQUIRE(smem <= 227 * 1024, "%s: %zu B of shared memory needed (A=%d, bins_per_range=%d) > 227 KB", name, smem, P.A, P.bpr);
+    cudaError_t e = cudaFuncSetAttribute(transient_kernel<MODE, BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    NLOS_REQUIRE(e == cudaSuccess, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e));
+    transient_kernel<MODE, BWD><<<n_cta_items, TR_WPB * 32, smem, s>>>(P);
+    NLOS_CHECK_LAUNCH(name);
+    return 0;
+}
+
+static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                       const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items, float t0, float dt,
+                       int T, int bins_per_range, int slice_len, float c_deltaT, float mcut, int mode)
+{
+    NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && A >= 1 && A <= 128, "transient: bad sizes");
+    NLOS_REQUIRE(bins_per_range > 0 && bins_per_range <= 256 && slice_len > 0, "transient: bad bins_per_range/slice_len");
+    NLOS_REQUIRE(mode == MODE_NUM || mode == MODE_ANA, "transient: mode must be 0 (numerical) or 1 (analytic-exact)");
+    NLOS_REQUIRE(tiles && records && list && cell_offsets && cell_counts && cell_sub_off && tile_items, "transient: null pointer");
+    NLOS_REQUIRE(((uintptr_t)tiles % 16) == 0 && ((uintptr_t)records % 16) == 0, "transient: tiles/records must be 16-byte aligned");
+    P.tiles = tiles; P.n_tiles = n_tiles; P.A = A; P.records = records; P.N = N; P.list = list;
+    P.cell_offsets = cell_offsets; P.cell_counts = cell_counts; P.cell_sub_off = cell_sub_off; P.tile_items = tile_items;
+    P.t0 = t0; P.dt = dt; P.inv_dt = 1.0f / dt; P.T = T; P.bpr = bins_per_range; P.n_ranges = (T + bins_per_range - 1) / bins_per_range;
+    P.slice_len = slice_len; P.flush_scale = mode == MODE_NUM ? c_deltaT : 1.0f; P.mcut2 = mcut * mcut;
+    P.H = nullptr; P.gH = nullptr; P.dacc = nullptr; P.counters = nullptr;
+    return 0;
+}
+
+extern "C" int nlosb200_transient_warps_per_block(void) { return TR_WPB; }
+
+extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                                          const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items,
+                                          int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float c_deltaT,
+                                          float mcut, int mode, float* H, void* stream)
+{
+    TransientParams P;
+    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, cell_offsets, cell_counts, cell_sub_off, tile_items, t0, dt, T, bins_per_range,
+                         slice_len, c_deltaT, mcut, mode);
+    if (rc) return rc;
+    NLOS_REQUIRE(H, "transient_forward: null H");
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(H, 0, (size_t)n_tiles * NLOS_TILE * T * sizeof(float), s);
+    NLOS_REQUIRE(e == cudaSuccess, "transient_forward: memset: %s", cudaGetErrorString(e));
+    if (n_cta_items <= 0) return 0;
+    P.H = H;
+    return mode == MODE_NUM ? launch_transient<MODE_NUM, false>(P, n_cta_items, s, "transient_kernel<num,fwd>")
+                            : launch_transient<MODE_ANA, false>(P, n_cta_items, s, "transient_kernel<ana,fwd>");
+}
+
+extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                                           const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items,
+                                           int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float c_deltaT,
+                                           float mcut, int mode, const float* grad_H, float* dacc, void* stream)
+{
+    TransientParams P;
+    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, cell_offsets, cell_counts, cell_sub_off, tile_items, t0, dt, T, bins_per_range,
+                         slice_len, c_deltaT, mcut, mode);
+    if (rc) return rc;
+    NLOS_REQUIRE(grad_H && dacc, "transient_backward: null pointer");
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(dacc, 0, (size_t)N * NLOS_GRAD_FLOATS * sizeof(float), s);
+    NLOS_REQUIRE(e == cudaSuccess, "transient_backward: memset: %s", cudaGetErrorString(e));
+    if (n_cta_items <= 0) return 0;
+    P.gH = grad_H;
+    P.dacc = dacc;
+    return mode == MODE_NUM ? launch_transient<MODE_NUM, true>(P, n_cta_items, s, "transient_kernel<num,bwd>")
+                            : launch_transient<MODE_ANA, true>(P, n_cta_items, s, "transient_kernel<ana,bwd>");
+}
+
+// work counters of SURVEY.md 8(d): counters[0] hit (g,ray) pairs, [1] W_s, [2] sample-evals this library evaluates, [3] W_b
+extern "C" int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                                        const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items,
+                                        int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float mcut,
+                                        unsigned long long* counters, void* stream)
+{
+    TransientParams P;
+    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, cell_offsets, cell_counts, cell_sub_off, tile_items, t0, dt, T, bins_per_range,
+                         slice_len, 1.0f, mcut, MODE_NUM);
+    if (rc) return rc;
+    NLOS_REQUIRE(counters, "transient_count: null counters");
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaError_t e = cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), s);
+    NLOS_REQUIRE(e == cudaSuccess, "transient_count: memset: %s", cudaGetErrorString(e));
+    if (n_cta_items <= 0) return 0;
+    P.counters = counters;
+    return launch_transient<MODE_COUNT, false>(P, n_cta_items, s, "transient_kernel<count>");
+}
