@@ -61,6 +61,7 @@ class ScanGeometry:
         th = torch.as_tensor(theta_range, dtype=torch.float32).reshape(S, 2).to(device)
         ph = torch.as_tensor(phi_range, dtype=torch.float32).reshape(S, 2).to(device)
         self.scan_o = sp.contiguous()
+        self.theta_range, self.phi_range = th, ph
         self.theta = torch_linspace_rows(th[:, 0], th[:, 1], self.A).contiguous()          # [S,A]
         self.phi = torch_linspace_rows(ph[:, 0], ph[:, 1], self.A).contiguous()
         self.sin_th, self.cos_th = torch.sin(self.theta).contiguous(), torch.cos(self.theta).contiguous()
@@ -104,6 +105,14 @@ class ScanGeometry:
         zs = torch.linspace(-extent / 2, extent / 2, Sy) if Sy > 1 else torch.zeros(1)
         pts = torch.stack([xs[None, :].expand(Sy, Sx), torch.zeros(Sy, Sx), zs[:, None].expand(Sy, Sx)], -1)
         return cls.from_volume(pts, volume_position, volume_size, A, tile=tile, device=device)
+
+    def rows(self, y0, y1):
+        """Sub-geometry of scan rows [y0, y1) -- the slab one GPU renders."""
+        sl = slice(y0 * self.Sx, y1 * self.Sx)
+        n = y1 - y0
+        return ScanGeometry(self.scan_o[sl].reshape(n, self.Sx, 3), self.theta_range[sl].reshape(n, self.Sx, 2),
+                            self.phi_range[sl].reshape(n, self.Sx, 2), self.A, vp_y=self.vp_y, tile=(self.tile_y, self.tile_x),
+                            device=self.device)
 
     # -- packing ---------------------------------------------------------------------------------
     def gather_tile_major(self, x):

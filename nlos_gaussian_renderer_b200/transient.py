@@ -108,22 +108,26 @@ class TransientRenderer:
         self.prepare(means, log_scales, rotations, opacities, features)
         return self.geom.untile(self.forward_tiled())
 
-    def backward_tiled(self, gH_tiled):
-        """dL/dH (tile-major) -> (d_means, d_log_scales, d_rotations, d_opacities, d_features)."""
+    def backward_tiled(self, gH_tiled, reduce_fn=None):
+        """dL/dH (tile-major) -> (d_means, d_log_scales, d_rotations, d_opacities, d_features).
+        reduce_fn(dacc) runs between the render backward and the per-Gaussian chain: the multi-GPU path
+        all-reduces the packed [N,16] buffer there (ONE NCCL all-reduce per fitting step)."""
         means, log_scales, rotations, opacities, features = self._params
         N = self._N
         gH_tiled = _f32c(gH_tiled)
         st = _lib.stream()
         _lib.call("nlosb200_transient_backward", *self._render_args(), self.c_deltaT, self.mcut, self.mode, gH_tiled.data_ptr(),
                   self.dacc.data_ptr(), st)
+        if reduce_fn is not None:
+            reduce_fn(self.dacc)
         outs = [torch.empty_like(means), torch.empty_like(log_scales), torch.empty_like(rotations), torch.empty_like(opacities),
                 torch.empty_like(features)]
         _lib.call("nlosb200_preprocess_backward", log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(), features.data_ptr(),
                   N, features.shape[1], self.mod, self.dacc.data_ptr(), *[o.data_ptr() for o in outs], 0, st)
         return tuple(outs)
 
-    def backward(self, gH):
-        return self.backward_tiled(self.geom.tile_grad(gH))
+    def backward(self, gH, reduce_fn=None):
+        return self.backward_tiled(self.geom.tile_grad(gH), reduce_fn)
 
     def count_work(self):
         """SURVEY.md 8(d) work counters for the prepared scene (dict)."""
