@@ -78,6 +78,41 @@ int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float
                              int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float mcut,
                              unsigned long long* counters, void* stream);
 
+/* ==== one-scan-point operators: the reference's pybind module nlos_gaussian_renderer._C ===========================
+ * (submodules/cuda_renderer/src/bindings.cpp:26-35).  A Python/torch caller allocates the outputs and passes
+ * data_ptr()s; see nlos_gaussian_renderer_b200/_C.py for the exact mirror of the three pybind signatures. */
+
+/* _C.filter_gaussians_per_ray (include/ray_aabb.h:7-13, src/ray_aabb.cu:10-102): per ray the ascending ids of the
+ * Gaussians whose AABB passes the slab test of cuda_utils.cuh:97-121, cut at `cap` (reference: 256).
+ * bboxes [N,6] 16-B aligned; out int32 [n_rays, cap+1], column 0 = count, unused slots = -1. */
+int nlosb200_filter_gaussians_per_ray(const float* ray_origins, const float* ray_directions, const float* bboxes, int n_rays,
+                                      int N, int cap, int* out, void* stream);
+/* per-scan-point albedo max(SH(dir(mean-cam))+0.5,0) into records[:,19] (volume_renderer.cu:107-111; CUDA sign convention of
+ * spherical_harmonics.cuh:20-80).  sh_dim < (degree+1)^2 is an error (the reference reads out of bounds). */
+int nlosb200_compat_albedo(const float* means, const float* features, const float* camera_pos, int N, int sh_dim,
+                           int sh_degree, float* records, void* stream);
+/* _C.render_rays (include/volume_renderer.h:8-24, src/volume_renderer.cu:16-305) after nlosb200_preprocess (records, bboxes with
+ * sigma 3.0 as volume_renderer.cu:232,244), nlosb200_compat_albedo and nlosb200_filter_gaussians_per_ray:
+ * rho_density, density, transmittance each [n_rays, T]. */
+int nlosb200_render_rays(const float* ray_origins, const float* ray_directions, const float* t_samples, const float* records,
+                         const int* filter, int cap, int n_rays, int T, int N, float c, float deltaT, int use_occlusion,
+                         float* rho_density, float* density, float* transmittance, void* stream);
+/* backward of render_rays -- CUDARenderFunction.backward (gaussian_model/cuda_autograd.py:110-191 returns zeros).
+ * grad_* [n_rays,T] nullable; rho_density/transmittance = saved forward outputs (needed with occlusion);
+ * dacc [N,16] (zeroed by the callee) -> nlosb200_preprocess_backward. */
+int nlosb200_render_rays_backward(const float* ray_origins, const float* ray_directions, const float* t_samples,
+                                  const float* records, const int* filter, int cap, int n_rays, int T, int N, float c,
+                                  float deltaT, int use_occlusion, const float* rho_density, const float* transmittance,
+                                  const float* grad_rho, const float* grad_density, const float* grad_transmittance, float* dacc,
+                                  void* stream);
+/* _C.render_rays_analytic (src/bindings.cpp:6-24, src/volume_renderer_analytic.cu:23-241): one scalar per ray;
+ * max_sections <= 128 (MAX_SECTIONS_PER_RAY). */
+int nlosb200_render_rays_analytic(const float* ray_origins, const float* ray_directions, float t_min, float t_max,
+                                  const int* filter, int cap, const float* means, const float* log_scales,
+                                  const float* rotations, const float* opacities, const float* features, const float* camera_pos,
+                                  int n_rays, int N, int sh_dim, int sh_degree, float scaling_modifier, float sigma_threshold,
+                                  int max_sections, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
