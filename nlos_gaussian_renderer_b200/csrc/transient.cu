@@ -12,11 +12,18 @@
 //   each warp owns a private [bins_per_range][32] shared-memory accumulator (bank == lane -> conflict free
 //   read-modify-write without atomics), gathers Gaussian records with per-record TMA bulk copies through a
 //   2-stage mbarrier ring, and flushes once per slice with coalesced float REDs.
-//   Per (Gaussian, scan point): conservative (theta,phi) footprint rectangle from the 3-sigma AABB, exact
-//   slab test per candidate ray (same predicate as cuda_utils.cuh:97-121), per hit ray the quadratic
-//   m2(r) = m2min + C (r - r*)^2 in centred form, then 1 MUFU.EX2 + 4 FP32 ops per (Gaussian, ray, bin).
-//   Backward: per ray three weighted moments of exp(-m2/2) in registers, chain rule to dL/dM, dL/dmu,
-//   dL/dop, dL/dalb per lane, ONE warp-shuffle reduction per (Gaussian, slice), 13 float REDs.
+//
+// Inner structure ("k-outer, rays in registers"), per (Gaussian, scan point):
+//   conservative (theta,phi) footprint rectangle from the 3-sigma AABB, walked in ROW CHUNKS of RC rays.  Per ray
+//   of a chunk: exact slab test (same predicate as cuda_utils.cuh:97-121), centred quadratic
+//   m2(r) = m2min + C (r - r*)^2, bin interval [klo,khi] of the 5.3-sigma cut.  Then ONE loop over the union of
+//   the chunk's bin intervals; inside it every ray advances  e_{k+1} = e_k g_k,  g_{k+1} = g_k q  (a Gaussian on a
+//   uniform grid is a second-order geometric recurrence, q = exp(-C dt^2)), re-seeded with MUFU.EX2 every TR_SEG
+//   bins: 2 FMUL + 1 FADD per sample-eval in the steady state and ONE shared-memory read-modify-write per
+//   (chunk, bin) instead of one per sample-eval.  Rays the recurrence cannot represent (seed underflow,
+//   Gaussians much narrower than a bin) take a direct 1-MUFU-per-bin path.
+//   Backward: per ray three moments  sum_k w_k e_k k^n  (n = 0,1,2)  in registers, chain rule to dL/dM, dL/dmu,
+//   dL/dop, dL/dalb per lane, ONE warp-shuffle reduction per (Gaussian, slice), 14 float REDs.
 #include "common.cuh"
 #include "../../include/nlosb200.h"
 
@@ -25,6 +32,7 @@ using namespace nlos;
 #define TR_WPB 8           // warps per CTA
 #define TR_RING 4          // records per ring stage
 #define TR_STAGES 2
+#define TR_SEG 16          // bins between MUFU re-seeds of a recurrence
 #define LOG2E_F 1.4426950408889634f
 #define TWO_OVER_SQRT_PI 1.1283791670955126f
 
@@ -60,10 +68,28 @@ __device__ __forceinline__ int clamp_floor(float x, int lo, int hi)
     x = floorf(x);
     return x <= (float)lo ? lo : (x >= (float)hi ? hi : (int)x);
 }
+// 1/x to ~1 ulp: MUFU.RCP + one Newton step instead of the ~10-instruction IEEE division
+__device__ __forceinline__ float rcp_nr(float x)
+{
+    float r = rcp_approx(x);
+    return r * fmaf(-x, r, 2.0f);
+}
+__device__ __forceinline__ float rsqrt_approx(float x)
+{
+    float y;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <int MODE, bool BWD>
+struct ChunkWidth {
+    static constexpr int value = (MODE == MODE_ANA && BWD) ? 2 : 4;     // rays per row chunk (register budget)
+};
 
 template <int MODE, bool BWD>
 __global__ void __launch_bounds__(TR_WPB * 32, 2) transient_kernel(const TransientParams P)
 {
+    constexpr int RC = ChunkWidth<MODE, BWD>::value;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int A = P.A;
     const int tile_floats = (NLOS_NTAB * A + NLOS_PINFO_ROWS) * NLOS_TILE;
@@ -136,8 +162,9 @@ __global__ void __launch_bounds__(TR_WPB * 32, 2) transient_kernel(const Transie
     const int flags = __float_as_int(s_pi[PI_FLAGS * 32 + lane]);
     const bool valid = flags & 1, fast = flags & 2;
     const float t0 = P.t0, dt = P.dt, inv_dt = P.inv_dt;
+    const float fRlo = (float)Rlo, fRhi = (float)Rhi;
     // radial extent of this warp's bins (bin k covers [t0+(k-.5)dt, t0+(k+.5)dt])
-    const float r_in = fmaf((float)Rlo - 0.5f, dt, t0), r_out = fmaf((float)Rhi + 0.5f, dt, t0);
+    const float r_in = fmaf(fRlo - 0.5f, dt, t0), r_out = fmaf(fRhi + 0.5f, dt, t0);
 
     if (MODE != MODE_COUNT) {
         if (!BWD) {
@@ -163,7 +190,10 @@ __global__ void __launch_bounds__(TR_WPB * 32, 2) transient_kernel(const Transie
     auto issue = [&](int b) {
         int stage = b & 1;
         int cnt = min(TR_RING, n - b * TR_RING);
-        if (lane == 0) mbar_arrive_expect_tx(&bar[stage], (uint32_t)cnt * NLOS_REC_FLOATS * 4u);
+        if (lane == 0) {
+            fence_proxy_async();
+            mbar_arrive_expect_tx(&bar[stage], (uint32_t)cnt * NLOS_REC_FLOATS * 4u);
+        }
         __syncwarp();
         gid_next = 0;
         if (lane < cnt) {
@@ -188,7 +218,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, 2) transient_kernel(const Transie
             float g00 = 0.f, g01 = 0.f, g02 = 0.f, g10 = 0.f, g11 = 0.f, g12 = 0.f, g20 = 0.f, g21 = 0.f, g22 = 0.f;   // sum dL/db (x) d
             float gwa = 0.f;                                                                        // dL/d(op*alb)
             const float cx = v0.x - ox, cy = v0.y - oy, cz = v0.z - oz;                             // mu - o
-            bool act = valid;
+            bool act = valid && (MODE == MODE_COUNT || opalb > 0.f);
             if (act) {
                 // radial reject of this scan point against the warp's bins
                 float D = sqrtf(cx * cx + cy * cy + cz * cz);
@@ -218,135 +248,272 @@ __global__ void __launch_bounds__(TR_WPB * 32, 2) transient_kernel(const Transie
                     }
                 }
                 int wb_lo = 0x7fffffff, wb_hi = -1;
+                const float dt2 = dt * dt;
                 for (int i = i0; i <= i1; ++i) {
                     const float sth = s_tab[(TAB_STH * A + i) * 32 + lane], cth = s_tab[(TAB_CTH * A + i) * 32 + lane];
                     const float tth = s_tab[(TAB_TTH * A + i) * 32 + lane];
                     const float tz0 = loz * tth, tz1 = hiz * tth;
                     const float zmn = fminf(tz0, tz1), zmx = fmaxf(tz0, tz1);
-                    for (int j = j0; j <= j1; ++j) {
-                        // slab test of cuda_utils.cuh:97-121 with every t multiplied by sin(theta) > 0
-                        const float icp = s_tab[(TAB_ICPH * A + j) * 32 + lane], isp = s_tab[(TAB_ISPH * A + j) * 32 + lane];
-                        const float tx0 = lox * icp, tx1 = hix * icp, ty0 = loy * isp, ty1 = hiy * isp;
-                        const float tmin = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), zmn);
-                        const float tmax = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), zmx);
-                        if (!(tmax >= tmin && tmax >= 0.f)) continue;
-                        const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
-                        const float dx = sth * cph, dy = sth * sph, dz = cth;
-                        const float bx = M00 * dx + M01 * dy + M02 * dz, by = M10 * dx + M11 * dy + M12 * dz,
-                                    bz = M20 * dx + M21 * dy + M22 * dz;                            // b = M d
-                        const float C = bx * bx + by * by + bz * bz;
-                        const float ab = ax * bx + ay * by + az * bz;
-                        const float rs = -ab / C;                                                   // closest approach r*
-                        const float px = fmaf(rs, bx, ax), py = fmaf(rs, by, ay), pz = fmaf(rs, bz, az);
-                        const float m2min = px * px + py * py + pz * pz;
-                        const float h2 = (P.mcut2 - m2min) / C;
-                        if (MODE == MODE_COUNT) {
-                            // slab interval stretched about its midpoint by 5.3/3 (t = t'/sin(theta))
-                            float ist = 1.0f / sth;
-                            float mid = 0.5f * (tmin + tmax) * ist, half = 0.5f * (tmax - tmin) * ist * (5.3f / 3.0f);
-                            int ka = clamp_ceil((mid - half - t0) * inv_dt, Rlo, Rhi + 1), kb = clamp_floor((mid + half - t0) * inv_dt, Rlo - 1, Rhi);
-                            c_hits += (r_in <= mid && mid < r_out) ? 1 : 0;
-                            if (kb >= ka) { c_ws += kb - ka + 1; wb_lo = min(wb_lo, ka); wb_hi = max(wb_hi, kb); }
-                        }
-                        if (!(h2 > 0.f)) continue;
-                        const float h = sqrtf(h2);
-                        int klo, khi;
-                        if (MODE == MODE_ANA) {
-                            klo = clamp_ceil((rs - h - t0) * inv_dt - 0.5f, Rlo, Rhi + 1);
-                            khi = clamp_floor((rs + h - t0) * inv_dt + 0.5f, Rlo - 1, Rhi);
-                        } else {
-                            klo = clamp_ceil((rs - h - t0) * inv_dt, Rlo, Rhi + 1);
-                            khi = clamp_floor((rs + h - t0) * inv_dt, Rlo - 1, Rhi);
-                        }
-                        if (klo > khi) continue;
-                        float* hp = Hw + (klo - Rlo) * NLOS_TILE + lane;
-                        const float wt = opalb * sth;
-                        if (MODE == MODE_COUNT) {
-                            c_ev += khi - klo + 1;
-                        } else if (MODE == MODE_NUM) {
-                            const float gam = -0.5f * LOG2E_F * C, al = -0.5f * LOG2E_F * m2min;
-                            float t = fmaf((float)klo, dt, t0) - rs;
-                            if (!BWD) {
-#pragma unroll 4
-                                for (int k = klo; k <= khi; ++k) {
-                                    float e = ex2_approx(fmaf(gam, t * t, al));
-                                    *hp = fmaf(wt, e, *hp);
-                                    hp += NLOS_TILE;
-                                    t += dt;
-                                }
-                            } else {
-                                float S0 = 0.f, S1 = 0.f, S2 = 0.f;
-#pragma unroll 4
-                                for (int k = klo; k <= khi; ++k) {
-                                    float we = *hp * ex2_approx(fmaf(gam, t * t, al));
-                                    float wet = we * t;
-                                    S0 += we;
-                                    S1 += wet;
-                                    S2 = fmaf(wet, t, S2);
-                                    hp += NLOS_TILE;
-                                    t += dt;
-                                }
-                                gwa = fmaf(sth, S0, gwa);
-                                // dL/da = -wt (S0 perp + S1 b) ; dL/db = -wt (r* (S0 perp + S1 b) + S1 perp + S2 b)
-                                const float ux = S0 * px + S1 * bx, uy = S0 * py + S1 * by, uz = S0 * pz + S1 * bz;
-                                const float vx = fmaf(rs, ux, S1 * px + S2 * bx), vy = fmaf(rs, uy, S1 * py + S2 * by),
-                                            vz = fmaf(rs, uz, S1 * pz + S2 * bz);
-                                gax = fmaf(-wt, ux, gax); gay = fmaf(-wt, uy, gay); gaz = fmaf(-wt, uz, gaz);
-                                const float bxw = -wt * vx, byw = -wt * vy, bzw = -wt * vz;
-                                g00 = fmaf(bxw, dx, g00); g01 = fmaf(bxw, dy, g01); g02 = fmaf(bxw, dz, g02);
-                                g10 = fmaf(byw, dx, g10); g11 = fmaf(byw, dy, g11); g12 = fmaf(byw, dz, g12);
-                                g20 = fmaf(bzw, dx, g20); g21 = fmaf(bzw, dy, g21); g22 = fmaf(bzw, dz, g22);
+                    // b = M d = cph * (sth M[:,0]) + sph * (sth M[:,1]) + cth M[:,2]
+                    const float s0x = sth * M00, s0y = sth * M10, s0z = sth * M20;
+                    const float s1x = sth * M01, s1y = sth * M11, s1z = sth * M21;
+                    const float c2x = cth * M02, c2y = cth * M12, c2z = cth * M22;
+                    const float wt = opalb * sth;
+                    for (int jc = j0; jc <= j1; jc += RC) {
+                        // ---- per-ray set-up of the chunk (fully unrolled, predicated)
+                        float rs[RC], gam[RC], al[RC], kl[RC], kh[RC];
+                        float kminf = 3.0e9f, kmaxf = -3.0e9f;
+#pragma unroll
+                        for (int u = 0; u < RC; ++u) {
+                            const int j = min(jc + u, j1);
+                            // slab test of cuda_utils.cuh:97-121 with every t multiplied by sin(theta) > 0
+                            const float icp = s_tab[(TAB_ICPH * A + j) * 32 + lane], isp = s_tab[(TAB_ISPH * A + j) * 32 + lane];
+                            const float tx0 = lox * icp, tx1 = hix * icp, ty0 = loy * isp, ty1 = hiy * isp;
+                            const float tmin = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), zmn);
+                            const float tmax = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), zmx);
+                            bool ok = (jc + u <= j1) && (tmax >= tmin) && (tmax >= 0.f);
+                            const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
+                            const float bx = fmaf(cph, s0x, fmaf(sph, s1x, c2x)), by = fmaf(cph, s0y, fmaf(sph, s1y, c2y)),
+                                        bz = fmaf(cph, s0z, fmaf(sph, s1z, c2z));
+                            const float C = bx * bx + by * by + bz * bz;
+                            const float ab = ax * bx + ay * by + az * bz;
+                            const float iC = rcp_nr(C);
+                            const float rsu = -ab * iC;                                             // closest approach r*
+                            const float px = fmaf(rsu, bx, ax), py = fmaf(rsu, by, ay), pz = fmaf(rsu, bz, az);
+                            const float m2min = px * px + py * py + pz * pz;
+                            const float h2 = (P.mcut2 - m2min) * iC;
+                            if (MODE == MODE_COUNT && ok) {
+                                // slab interval stretched about its midpoint by 5.3/3 (t = t'/sin(theta))
+                                float ist = 1.0f / sth;
+                                float mid = 0.5f * (tmin + tmax) * ist, half = 0.5f * (tmax - tmin) * ist * (5.3f / 3.0f);
+                                int ka = clamp_ceil((mid - half - t0) * inv_dt, Rlo, Rhi + 1), kb = clamp_floor((mid + half - t0) * inv_dt, Rlo - 1, Rhi);
+                                c_hits += (r_in <= mid && mid < r_out) ? 1 : 0;
+                                if (kb >= ka) { c_ws += kb - ka + 1; wb_lo = min(wb_lo, ka); wb_hi = max(wb_hi, kb); }
                             }
-                        } else {   // MODE_ANA : exact bin integrals, erf shared between adjacent bin edges
-                            const float sq = sqrtf(0.5f * C);
-                            const float pref = sqrtf(1.5707963267948966f / C) * ex2_approx(-0.5f * LOG2E_F * m2min);
-                            float u = fmaf((float)klo - 0.5f, dt, t0) - rs;   // lower edge of bin klo, relative to r*
-                            float z = sq * u;
-                            const float dz_ = sq * dt;
-                            float Ep = erf_fast(z);
-                            if (!BWD) {
-                                const float wa = wt * pref;
+                            ok = ok && (h2 > 0.f);
+                            const float hh = h2 * rsqrt_approx(fmaxf(h2, 1e-30f)) * inv_dt;          // half width of the cut in bins
+                            const float xc = (rsu - t0) * inv_dt;
+                            const float off = (MODE == MODE_ANA) ? 0.5f : 0.0f;                        // bins are [k-.5, k+.5] for the integral
+                            float klu = fmaxf(ceilf(xc - hh - off), fRlo), khu = fminf(floorf(xc + hh + off), fRhi);
+                            ok = ok && (klu <= khu);
+                            rs[u] = rsu;
+                            gam[u] = -0.5f * LOG2E_F * C;
+                            al[u] = -0.5f * LOG2E_F * m2min;
+                            kl[u] = ok ? klu : 3.0e9f;
+                            kh[u] = ok ? khu : -3.0e9f;
+                            kminf = fminf(kminf, kl[u]);
+                            kmaxf = fmaxf(kmaxf, kh[u]);
+                        }
+                        if (kminf > kmaxf) continue;
+                        const int kmin = (int)kminf, kmax = (int)kmaxf;
+                        const float tk0 = fmaf(kminf, dt, t0);
+                        float* const hp0 = Hw + (kmin - Rlo) * NLOS_TILE + lane;
+                        if (MODE == MODE_COUNT) {
+#pragma unroll
+                            for (int u = 0; u < RC; ++u)
+                                if (kl[u] <= kh[u]) c_ev += (unsigned long long)(kmax - kmin + 1);
+                        } else if (MODE == MODE_NUM) {
+                            // ---- numerical mode: recurrence  e_{k+1} = e_k g_k ; g_{k+1} = g_k q   per ray, common bin loop
+                            float e[RC], g[RC], qq[RC];
+                            float S0[RC], S1[RC], S2[RC];
+                            bool fr[RC];
+                            bool anyfast = false, anyslow = false;
+#pragma unroll
+                            for (int u = 0; u < RC; ++u) {
+                                const float tu = tk0 - rs[u];
+                                const float L = fmaf(gam[u] * tu, tu, al[u]);
+                                const bool vu = kl[u] <= kh[u];
+                                fr[u] = vu && (L > -100.f) && (gam[u] * dt2 > -6.f);     // seed representable, recurrence well-conditioned
+                                anyfast = anyfast || fr[u];
+                                anyslow = anyslow || (vu && !fr[u]);
+                                qq[u] = ex2_approx(2.0f * gam[u] * dt2);
+                                S0[u] = 0.f; S1[u] = 0.f; S2[u] = 0.f;
+                            }
+                            const float kfc = 0.5f * (kmaxf - kminf);                    // moments are taken about the middle of the chunk's bins
+                            if (anyfast) {
+                                float* hp = hp0;
+                                float kf = -kfc;
+                                for (int ks = kmin; ks <= kmax; ks += TR_SEG) {
+                                    const int nseg = min(TR_SEG, kmax - ks + 1);
+                                    const float tks = fmaf((float)ks, dt, t0);
+#pragma unroll
+                                    for (int u = 0; u < RC; ++u) {
+                                        const float tu = tks - rs[u];
+                                        const float gt = gam[u] * tu;
+                                        const float ev = ex2_approx(fmaf(gt, tu, al[u]));
+                                        const float gv = ex2_approx(fmaf(2.0f * gt, dt, gam[u] * dt2));
+                                        e[u] = fr[u] ? (BWD ? ev : wt * ev) : 0.f;
+                                        g[u] = fr[u] ? gv : 0.f;
+                                    }
+                                    if (!BWD) {
+#pragma unroll 4
+                                        for (int kk = 0; kk < nseg; ++kk) {
+                                            float acc = 0.f;
+#pragma unroll
+                                            for (int u = 0; u < RC; ++u) { acc += e[u]; e[u] *= g[u]; g[u] *= qq[u]; }
+                                            *hp += acc;
+                                            hp += NLOS_TILE;
+                                        }
+                                    } else {
 #pragma unroll 2
-                                for (int k = klo; k <= khi; ++k) {
-                                    z += dz_;
-                                    float E = erf_fast(z);
-                                    *hp = fmaf(wa, E - Ep, *hp);
-                                    Ep = E;
-                                    hp += NLOS_TILE;
+                                        for (int kk = 0; kk < nseg; ++kk) {
+                                            const float w = *hp;
+#pragma unroll
+                                            for (int u = 0; u < RC; ++u) {
+                                                const float we = w * e[u], wk = we * kf;
+                                                S0[u] += we;
+                                                S1[u] += wk;
+                                                S2[u] = fmaf(wk, kf, S2[u]);
+                                                e[u] *= g[u];
+                                                g[u] *= qq[u];
+                                            }
+                                            kf += 1.0f;
+                                            hp += NLOS_TILE;
+                                        }
+                                    }
                                 }
-                            } else {
-                                float F = 0.f, P1 = 0.f, P2 = 0.f;
-                                float Dp = TWO_OVER_SQRT_PI * ex2_approx(-LOG2E_F * z * z);
-                                float DUp = Dp * u;
+                            }
+                            if (BWD) {
+                                // moments about the chunk centre -> moments of tau = r_k - r*
+                                const float tcen = fmaf(kfc, dt, tk0);
+#pragma unroll
+                                for (int u = 0; u < RC; ++u) {
+                                    const float tc = tcen - rs[u];
+                                    const float m0 = S0[u], m1 = S1[u] * dt, m2 = S2[u] * dt2;
+                                    S1[u] = fmaf(tc, m0, m1);
+                                    S2[u] = fmaf(tc, fmaf(tc, m0, 2.0f * m1), m2);
+                                }
+                            }
+                            if (anyslow) {
+                                // direct evaluation, 1 MUFU per bin, for rays the recurrence cannot carry
+#pragma unroll
+                                for (int u = 0; u < RC; ++u) {
+                                    if (!(kl[u] <= kh[u]) || fr[u]) continue;
+                                    const int klo = (int)kl[u], khi = (int)kh[u];
+                                    float* hp = Hw + (klo - Rlo) * NLOS_TILE + lane;
+                                    float t = fmaf((float)klo, dt, t0) - rs[u];
+                                    float a0 = 0.f, a1 = 0.f, a2 = 0.f;
+                                    for (int k = klo; k <= khi; ++k) {
+                                        const float ev = ex2_approx(fmaf(gam[u], t * t, al[u]));
+                                        if (!BWD) {
+                                            *hp = fmaf(wt, ev, *hp);
+                                        } else {
+                                            const float we = *hp * ev, wet = we * t;
+                                            a0 += we; a1 += wet; a2 = fmaf(wet, t, a2);
+                                        }
+                                        hp += NLOS_TILE;
+                                        t += dt;
+                                    }
+                                    if (BWD) { S0[u] = a0; S1[u] = a1; S2[u] = a2; }
+                                }
+                            }
+                            if (BWD) {
+#pragma unroll
+                                for (int u = 0; u < RC; ++u) {
+                                    if (!(kl[u] <= kh[u])) continue;
+                                    const int j = jc + u;
+                                    const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
+                                    const float bx = fmaf(cph, s0x, fmaf(sph, s1x, c2x)), by = fmaf(cph, s0y, fmaf(sph, s1y, c2y)),
+                                                bz = fmaf(cph, s0z, fmaf(sph, s1z, c2z));
+                                    const float px = fmaf(rs[u], bx, ax), py = fmaf(rs[u], by, ay), pz = fmaf(rs[u], bz, az);
+                                    const float dx = sth * cph, dy = sth * sph, dz = cth;
+                                    gwa = fmaf(sth, S0[u], gwa);
+                                    // dL/da = -wt (S0 perp + S1 b) ; dL/db = -wt (r* (S0 perp + S1 b) + S1 perp + S2 b)
+                                    const float ux = S0[u] * px + S1[u] * bx, uy = S0[u] * py + S1[u] * by, uz = S0[u] * pz + S1[u] * bz;
+                                    const float vx = fmaf(rs[u], ux, S1[u] * px + S2[u] * bx), vy = fmaf(rs[u], uy, S1[u] * py + S2[u] * by),
+                                                vz = fmaf(rs[u], uz, S1[u] * pz + S2[u] * bz);
+                                    gax = fmaf(-wt, ux, gax); gay = fmaf(-wt, uy, gay); gaz = fmaf(-wt, uz, gaz);
+                                    const float bxw = -wt * vx, byw = -wt * vy, bzw = -wt * vz;
+                                    g00 = fmaf(bxw, dx, g00); g01 = fmaf(bxw, dy, g01); g02 = fmaf(bxw, dz, g02);
+                                    g10 = fmaf(byw, dx, g10); g11 = fmaf(byw, dy, g11); g12 = fmaf(byw, dz, g12);
+                                    g20 = fmaf(bzw, dx, g20); g21 = fmaf(bzw, dy, g21); g22 = fmaf(bzw, dz, g22);
+                                }
+                            }
+                        } else {
+                            // ---- MODE_ANA : exact bin integrals, erf shared between adjacent bin edges
+                            float sq[RC], pref[RC], u0[RC], Ep[RC];
+                            float Dp[RC], DUp[RC], F[RC], P1[RC], P2[RC];
+                            const float ue = fmaf(-0.5f, dt, tk0);                           // lower edge of bin kmin
+#pragma unroll
+                            for (int u = 0; u < RC; ++u) {
+                                const bool vu = kl[u] <= kh[u];
+                                const float C = gam[u] * (-2.0f / LOG2E_F);
+                                sq[u] = vu ? sqrtf(0.5f * C) : 0.f;
+                                pref[u] = vu ? 1.2533141373155001f * rsqrt_approx(C) * ex2_approx(al[u]) : 0.f;     // sqrt(pi/(2C)) e^{-m2min/2}
+                                u0[u] = ue - rs[u];
+                                const float z = sq[u] * u0[u];
+                                Ep[u] = erf_fast(z);
+                                if (BWD) {
+                                    Dp[u] = TWO_OVER_SQRT_PI * ex2_approx(-LOG2E_F * z * z);
+                                    DUp[u] = Dp[u] * u0[u];
+                                    F[u] = 0.f; P1[u] = 0.f; P2[u] = 0.f;
+                                }
+                            }
+                            {
+                                float* hp = hp0;
+                                float kf = 1.0f;
+                                if (!BWD) {
 #pragma unroll 2
-                                for (int k = klo; k <= khi; ++k) {
-                                    z += dz_;
-                                    u += dt;
-                                    float E = erf_fast(z);
-                                    float Dn = TWO_OVER_SQRT_PI * ex2_approx(-LOG2E_F * z * z);
-                                    float DUn = Dn * u;
-                                    float w = *hp;
-                                    F = fmaf(w, E - Ep, F);
-                                    P1 = fmaf(w, Dn - Dp, P1);
-                                    P2 = fmaf(w, DUn - DUp, P2);
-                                    Ep = E; Dp = Dn; DUp = DUn;
-                                    hp += NLOS_TILE;
+                                    for (int k = kmin; k <= kmax; ++k) {
+                                        float acc = 0.f;
+#pragma unroll
+                                        for (int u = 0; u < RC; ++u) {
+                                            const float E = erf_fast(sq[u] * fmaf(kf, dt, u0[u]));
+                                            acc = fmaf(wt * pref[u], E - Ep[u], acc);
+                                            Ep[u] = E;
+                                        }
+                                        *hp += acc;
+                                        hp += NLOS_TILE;
+                                        kf += 1.0f;
+                                    }
+                                } else {
+                                    for (int k = kmin; k <= kmax; ++k) {
+                                        const float w = *hp;
+#pragma unroll
+                                        for (int u = 0; u < RC; ++u) {
+                                            const float uu = fmaf(kf, dt, u0[u]);
+                                            const float z = sq[u] * uu;
+                                            const float E = erf_fast(z);
+                                            const float Dn = TWO_OVER_SQRT_PI * ex2_approx(-LOG2E_F * z * z);
+                                            const float DUn = Dn * uu;
+                                            F[u] = fmaf(w, E - Ep[u], F[u]);
+                                            P1[u] = fmaf(w, Dn - Dp[u], P1[u]);
+                                            P2[u] = fmaf(w, DUn - DUp[u], P2[u]);
+                                            Ep[u] = E; Dp[u] = Dn; DUp[u] = DUn;
+                                        }
+                                        hp += NLOS_TILE;
+                                        kf += 1.0f;
+                                    }
                                 }
-                                gwa = fmaf(sth * pref, F, gwa);
-                                const float iC = 1.0f / C;
-                                const float gpref = wt * F, gsq = wt * pref * P2, grs = -wt * pref * sq * P1;
-                                const float gm = -0.5f * gpref * pref;
-                                const float k1 = grs * iC;                                  // multiplies (perp + r* b) and b
-                                const float k2 = gsq / (2.0f * sq) - gpref * pref * iC;     // multiplies b
-                                // dL/da = 2 gm perp - k1 b ;  dL/db = 2 gm r* perp - k1 (perp + r* b) + k2 b
-                                const float dax = 2.f * gm * px - k1 * bx, day = 2.f * gm * py - k1 * by, daz = 2.f * gm * pz - k1 * bz;
-                                const float dbx = 2.f * gm * rs * px - k1 * fmaf(rs, bx, px) + k2 * bx;
-                                const float dby = 2.f * gm * rs * py - k1 * fmaf(rs, by, py) + k2 * by;
-                                const float dbz = 2.f * gm * rs * pz - k1 * fmaf(rs, bz, pz) + k2 * bz;
-                                gax += dax; gay += day; gaz += daz;
-                                g00 = fmaf(dbx, dx, g00); g01 = fmaf(dbx, dy, g01); g02 = fmaf(dbx, dz, g02);
-                                g10 = fmaf(dby, dx, g10); g11 = fmaf(dby, dy, g11); g12 = fmaf(dby, dz, g12);
-                                g20 = fmaf(dbz, dx, g20); g21 = fmaf(dbz, dy, g21); g22 = fmaf(dbz, dz, g22);
+                            }
+                            if (BWD) {
+#pragma unroll
+                                for (int u = 0; u < RC; ++u) {
+                                    if (!(kl[u] <= kh[u])) continue;
+                                    const int j = jc + u;
+                                    const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
+                                    const float bx = fmaf(cph, s0x, fmaf(sph, s1x, c2x)), by = fmaf(cph, s0y, fmaf(sph, s1y, c2y)),
+                                                bz = fmaf(cph, s0z, fmaf(sph, s1z, c2z));
+                                    const float rsu = rs[u];
+                                    const float px = fmaf(rsu, bx, ax), py = fmaf(rsu, by, ay), pz = fmaf(rsu, bz, az);
+                                    const float dx = sth * cph, dy = sth * sph, dz = cth;
+                                    const float C = gam[u] * (-2.0f / LOG2E_F);
+                                    gwa = fmaf(sth * pref[u], F[u], gwa);
+                                    const float iC = 1.0f / C;
+                                    const float gpref = wt * F[u], gsq = wt * pref[u] * P2[u], grs = -wt * pref[u] * sq[u] * P1[u];
+                                    const float gm = -0.5f * gpref * pref[u];
+                                    const float k1 = grs * iC;                                  // multiplies (perp + r* b) and b
+                                    const float k2 = gsq / (2.0f * sq[u]) - gpref * pref[u] * iC;     // multiplies b
+                                    // dL/da = 2 gm perp - k1 b ;  dL/db = 2 gm r* perp - k1 (perp + r* b) + k2 b
+                                    const float dax = 2.f * gm * px - k1 * bx, day = 2.f * gm * py - k1 * by, daz = 2.f * gm * pz - k1 * bz;
+                                    const float dbx = 2.f * gm * rsu * px - k1 * fmaf(rsu, bx, px) + k2 * bx;
+                                    const float dby = 2.f * gm * rsu * py - k1 * fmaf(rsu, by, py) + k2 * by;
+                                    const float dbz = 2.f * gm * rsu * pz - k1 * fmaf(rsu, bz, pz) + k2 * bz;
+                                    gax += dax; gay += day; gaz += daz;
+                                    g00 = fmaf(dbx, dx, g00); g01 = fmaf(dbx, dy, g01); g02 = fmaf(dbx, dz, g02);
+                                    g10 = fmaf(dby, dx, g10); g11 = fmaf(dby, dy, g11); g12 = fmaf(dby, dz, g12);
+                                    g20 = fmaf(dbz, dx, g20); g21 = fmaf(dbz, dy, g21); g22 = fmaf(dbz, dz, g22);
+                                }
                             }
                         }
                     }
