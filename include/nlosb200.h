@@ -49,34 +49,35 @@ int nlosb200_build_scan_tiles(const float* scan_o, const float* sin_th, const fl
                               const float* cos_ph, const float* lattice, const float* hscale, const int* valid, int S, int A,
                               float* tiles, void* stream);
 
-/* ---- shell-intersection binning (replaces filter_gaussians_kernel, src/ray_aabb.cu:10-102, as the
- * culling structure of the batched renderer).  n_ranges = ceil(T/bins_per_range) <= 64, n_cells = n_tiles*n_ranges.
- * chunk_counts int32 [n_cells * nlosb200_bin_num_chunks(N)], cell_counts int32 [n_cells],
- * cell_offsets int64 [n_cells+1], cell_sub_off int32 [n_cells], tile_items int32 [n_tiles+1],
- * header int64 [4] = {total list entries, CTA work items, overflow flag, -}. */
-int nlosb200_bin_shells_plan(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                             int bins_per_range, int slice_len, int warps_per_block, int* chunk_counts, int* cell_counts,
-                             long long* cell_offsets, int* cell_sub_off, int* tile_items, long long* header, void* stream);
-int nlosb200_bin_shells_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                             int bins_per_range, const int* chunk_counts_scanned, const long long* cell_offsets, int* list,
+/* ---- window binning (replaces filter_gaussians_kernel, src/ray_aabb.cu:10-102, as the culling structure of the batched
+ * renderer).  Per (tile, Gaussian) the conservative radial shell is an inclusive bin interval [klo,khi]; the renderer's
+ * accumulator is a sliding window of `window` bins (power of two) advancing in steps of `bucket` bins, so a Gaussian is
+ * listed once per tile unless its interval is longer than L = window-bucket (then entry e covers [klo+eL, klo+(e+1)L-1]).
+ * Entry (g,e) lives in cell (tile, (klo+eL)/bucket); list value = g | e<<26; per cell ascending g.
+ * n_buckets = ceil(T/bucket) <= 64, n_cells = n_tiles*n_buckets.
+ * chunk_counts int32 [n_cells * nlosb200_bin_num_chunks(N)], cell_counts int32 [n_cells], cell_offsets int64 [n_cells+1],
+ * tile_items int32 [n_tiles+1], header int64 [4] = {total list entries, CTA work items, overflow flag, -}. */
+int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
+                             int window, int bucket, int slice_len, int warps_per_block, int* chunk_counts, int* cell_counts,
+                             long long* cell_offsets, int* tile_items, long long* header, void* stream);
+int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
+                             int window, int bucket, const int* chunk_counts_scanned, const long long* cell_offsets, int* list,
                              long long list_capacity, long long* header, void* stream);
 
 /* ---- batched transient H[n_tiles*32, T] and its backward.  mode 0 = numerical (volume_renderer.cu
  * no-occlusion branch :139-182), 1 = analytic-exact per-bin integral.
  * bin k sits at radius t0 + k*dt.  H and dacc are zeroed by the callee. */
 int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                               const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items,
-                               int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float c_deltaT,
-                               float mcut, int mode, float* H, void* stream);
+                               const long long* cell_offsets, const int* tile_items, int n_cta_items, float t0, float dt, int T,
+                               int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, float* H, void* stream);
 int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items,
-                                int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float c_deltaT,
-                                float mcut, int mode, const float* grad_H, float* dacc, void* stream);
+                                const long long* cell_offsets, const int* tile_items, int n_cta_items, float t0, float dt, int T,
+                                int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, const float* grad_H,
+                                float* dacc, void* stream);
 /* counters uint64 [4]: hit (g,ray) pairs, W_s, sample-evals evaluated, W_b */
 int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                             const long long* cell_offsets, const int* cell_counts, const int* cell_sub_off, const int* tile_items,
-                             int n_cta_items, float t0, float dt, int T, int bins_per_range, int slice_len, float mcut,
-                             unsigned long long* counters, void* stream);
+                             const long long* cell_offsets, const int* tile_items, int n_cta_items, float t0, float dt, int T,
+                             int window, int bucket, int slice_len, float mcut, unsigned long long* counters, void* stream);
 
 /* ==== one-scan-point operators: the reference's pybind module nlos_gaussian_renderer._C ===========================
  * (submodules/cuda_renderer/src/bindings.cpp:26-35).  A Python/torch caller allocates the outputs and passes

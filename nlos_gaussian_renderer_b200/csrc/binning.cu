@@ -1,18 +1,22 @@
-// binning.cu -- shell-intersection culling / binning of Gaussians per (scan tile x time-bin range).
+// binning.cu -- window binning of Gaussians per scan tile for the batched transient renderer.
 //
 // Replaces the reference's brute-force per-ray AABB filter as the culling structure of the batched
 // renderer (/root/reference/submodules/cuda_renderer/src/ray_aabb.cu:10-102 is O(N_rays * N) and caps
 // every ray at 256 Gaussians).  In confocal NLOS every scan point's angular lattice covers the whole
-// hidden volume, so the only effective cull is radial: Gaussian g belongs to cell (tile, range) iff
-// its conservative shell  [ sqrt(min_p |mu-o_p|^2) - rad , sqrt(max_p |mu-o_p|^2) + rad ]  seen from
-// the tile's scan points intersects the range's bins.  The definition (and the bit-exact operation
-// order) is oracle/nlos_oracle.c:orc_shell_intervals / orc_shell_lists; lists are ascending in g.
+// hidden volume, so the only effective cull is radial: per (tile, Gaussian) the conservative shell
+//   [ sqrt(min_p |mu-o_p|^2) - rad , sqrt(max_p |mu-o_p|^2) + rad ]   (p over the tile's scan points)
+// is converted to an inclusive bin interval [klo, khi].  The render kernel accumulates into a sliding window of
+// `window` bins that advances in steps of `bucket` bins, so a Gaussian is listed ONCE per tile (entry e = 0) unless
+// its interval is longer than L = window - bucket, in which case entry e covers [klo + e L, klo + (e+1) L - 1].
+// Entry (g, e) lives in cell (tile, (klo + e L) / bucket); per cell the entries are ascending in g; the list value
+// is g | e << 26.  Definition and bit-exact operation order: oracle/nlos_oracle.c:orc_shell_bins and
+// oracle/__init__.py:window_lists.
 //
 // Passes (all stream ordered, no host sync inside):
-//   count : per (tile, chunk of 1024 Gaussians) histogram of range membership
-//   scan  : per cell exclusive scan over chunks; then over cells (int64 offsets), and the render
-//           work decomposition (sub-items of <= slice_len list entries, CTA items of warps_per_block)
-//   fill  : ordered (ballot-ranked) scatter of Gaussian ids into the cell lists
+//   count : per (tile, chunk of 1024 Gaussians) histogram of cell membership
+//   scan  : per cell exclusive scan over chunks; then over cells (int64 offsets), and the render work
+//           decomposition (per tile: slices of slice_len entries, CTA items of warps_per_block slices)
+//   fill  : ordered (ballot-ranked) scatter of entries into the cell lists
 #include "common.cuh"
 #include "../../include/nlosb200.h"
 
@@ -41,9 +45,8 @@ __device__ __forceinline__ void load_tile_points(TilePoints& tp, const float* __
     }
 }
 
-// oracle/nlos_oracle.c:orc_shell_intervals, same single-rounding operation order
-__device__ __forceinline__ void shell_interval(const TilePoints& tp, float4 sh, float t0, float inv_dt, int T, int bpr, int n_ranges,
-                                               int& lo, int& hi)
+// oracle/nlos_oracle.c:orc_shell_bins, same single-rounding operation order.  klo > khi = empty.
+__device__ __forceinline__ void shell_bins(const TilePoints& tp, float4 sh, float t0, float inv_dt, int T, int& klo, int& khi)
 {
     float d2min = INFINITY, d2max = 0.0f;
 #pragma unroll 8
@@ -57,20 +60,23 @@ __device__ __forceinline__ void shell_interval(const TilePoints& tp, float4 sh, 
     float rlo = __fsub_rn(__fsqrt_rn(d2min), sh.w), rhi = __fadd_rn(__fsqrt_rn(d2max), sh.w);
     float klo_f = floorf(__fadd_rn(__fmul_rn(__fsub_rn(rlo, t0), inv_dt), 0.5f));
     float khi_f = floorf(__fadd_rn(__fmul_rn(__fsub_rn(rhi, t0), inv_dt), 0.5f));
-    int klo = klo_f < 0.0f ? 0 : (klo_f > (float)(T - 1) ? T : (int)klo_f);
-    int khi = khi_f < 0.0f ? -1 : (khi_f > (float)(T - 1) ? T - 1 : (int)khi_f);
-    if (klo > khi) {
-        lo = 1;
-        hi = 0;
-    } else {
-        lo = klo / bpr;
-        hi = khi / bpr;
-        if (hi >= n_ranges) hi = n_ranges - 1;
-    }
+    klo = klo_f < 0.0f ? 0 : (klo_f > (float)(T - 1) ? T : (int)klo_f);
+    khi = khi_f < 0.0f ? -1 : (khi_f > (float)(T - 1) ? T - 1 : (int)khi_f);
+}
+
+// sub-interval index e of the entry of [klo, khi] that lives in bucket r, or -1  (L > bucket => at most one)
+__device__ __forceinline__ int entry_in_bucket(int klo, int khi, int r, int L, int bucket)
+{
+    if (klo > khi) return -1;
+    int top = r * bucket + bucket - 1 - klo;          // last bin of the bucket, relative to klo
+    if (top < 0) return -1;
+    int e = top / L;
+    int s = klo + e * L;
+    return (s <= khi && s >= r * bucket) ? e : -1;
 }
 
 __global__ void __launch_bounds__(BIN_THREADS) shell_count_kernel(const float* __restrict__ tiles, int A, const float4* __restrict__ shell, int N,
-                                                                  float t0, float inv_dt, int T, int bpr, int n_ranges, int n_chunks,
+                                                                  float t0, float inv_dt, int T, int L, int bucket, int n_buckets, int n_chunks,
                                                                   int* __restrict__ chunk_counts)
 {
     __shared__ TilePoints tp;
@@ -83,13 +89,13 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_count_kernel(const float* _
     for (int j = 0; j < BIN_GPT; ++j) {
         int g = chunk * BIN_CHUNK + j * BIN_THREADS + threadIdx.x;
         if (g < N) {
-            int lo, hi;
-            shell_interval(tp, shell[g], t0, inv_dt, T, bpr, n_ranges, lo, hi);
-            for (int r = lo; r <= hi; ++r) atomicAdd(&cnt[r], 1);
+            int klo, khi;
+            shell_bins(tp, shell[g], t0, inv_dt, T, klo, khi);
+            for (int s = klo; s <= khi; s += L) atomicAdd(&cnt[s / bucket], 1);
         }
     }
     __syncthreads();
-    if (threadIdx.x < n_ranges) chunk_counts[((size_t)tile * n_ranges + threadIdx.x) * n_chunks + chunk] = cnt[threadIdx.x];
+    if (threadIdx.x < n_buckets) chunk_counts[((size_t)tile * n_buckets + threadIdx.x) * n_chunks + chunk] = cnt[threadIdx.x];
 }
 
 // per cell: exclusive scan over chunks (in place) and the cell total
@@ -114,15 +120,15 @@ __global__ void __launch_bounds__(256) scan_chunks_kernel(int* __restrict__ chun
     for (int i = b; i < e; ++i) { int v = row[i]; row[i] = run; run += v; }
 }
 
-// single CTA: cell offsets (int64), per-tile sub-item prefix, CTA-item prefix, header
+// single CTA: cell offsets (int64), CTA-item prefix per tile, header
 //   header[0] = total list entries, header[1] = number of CTA work items, header[2] = overflow flag (set by fill)
-__global__ void __launch_bounds__(1024) scan_cells_kernel(const int* __restrict__ cell_counts, int n_tiles, int n_ranges, int slice_len, int wpb,
-                                                          long long* __restrict__ cell_offsets, int* __restrict__ cell_sub_off,
-                                                          int* __restrict__ tile_items, long long* __restrict__ header)
+__global__ void __launch_bounds__(1024) scan_cells_kernel(const int* __restrict__ cell_counts, int n_tiles, int n_buckets, int slice_len, int wpb,
+                                                          long long* __restrict__ cell_offsets, int* __restrict__ tile_items,
+                                                          long long* __restrict__ header)
 {
     __shared__ long long part[1024];
     __shared__ int parti[1024];
-    int n_cells = n_tiles * n_ranges;
+    int n_cells = n_tiles * n_buckets;
     {
         int seg = (n_cells + 1023) / 1024;
         int b = threadIdx.x * seg, e = min(b + seg, n_cells);
@@ -142,17 +148,17 @@ __global__ void __launch_bounds__(1024) scan_cells_kernel(const int* __restrict_
         for (int i = b; i < e; ++i) { cell_offsets[i] = run; run += cell_counts[i]; }
     }
     {
+        // a tile's entries are contiguous and ordered by bucket; slices of slice_len entries, wpb slices per CTA item
         int seg = (n_tiles + 1023) / 1024;
         int b = threadIdx.x * seg, e = min(b + seg, n_tiles);
+        auto items_of = [&](int t) {
+            long long tot = 0;
+            for (int r = 0; r < n_buckets; ++r) tot += cell_counts[t * n_buckets + r];
+            long long nsub = (tot + slice_len - 1) / slice_len;
+            return (int)((nsub + wpb - 1) / wpb);
+        };
         int s = 0;
-        for (int t = b; t < e; ++t) {
-            int nsub = 0;
-            for (int r = 0; r < n_ranges; ++r) {
-                cell_sub_off[t * n_ranges + r] = nsub;
-                nsub += (cell_counts[t * n_ranges + r] + slice_len - 1) / slice_len;
-            }
-            s += (nsub + wpb - 1) / wpb;
-        }
+        for (int t = b; t < e; ++t) s += items_of(t);
         parti[threadIdx.x] = s;
         __syncthreads();
         if (threadIdx.x == 0) {
@@ -163,19 +169,14 @@ __global__ void __launch_bounds__(1024) scan_cells_kernel(const int* __restrict_
         }
         __syncthreads();
         int run = parti[threadIdx.x];
-        for (int t = b; t < e; ++t) {
-            tile_items[t] = run;
-            int nsub = 0;
-            for (int r = 0; r < n_ranges; ++r) nsub += (cell_counts[t * n_ranges + r] + slice_len - 1) / slice_len;
-            run += (nsub + wpb - 1) / wpb;
-        }
+        for (int t = b; t < e; ++t) { tile_items[t] = run; run += items_of(t); }
     }
 }
 
 __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __restrict__ tiles, int A, const float4* __restrict__ shell, int N,
-                                                                 float t0, float inv_dt, int T, int bpr, int n_ranges, int n_chunks,
+                                                                 float t0, float inv_dt, int T, int L, int bucket, int n_buckets, int n_chunks,
                                                                  const int* __restrict__ chunk_off, const long long* __restrict__ cell_offsets,
-                                                                 int* __restrict__ list, long long capacity, long long* __restrict__ header)
+                                                                 unsigned* __restrict__ list, long long capacity, long long* __restrict__ header)
 {
     __shared__ TilePoints tp;
     __shared__ int wc[BIN_GPT][BIN_THREADS / 32][BIN_MAX_RANGES];
@@ -189,16 +190,16 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __
         int g = chunk * BIN_CHUNK + j * BIN_THREADS + threadIdx.x;
         lo[j] = 1;
         hi[j] = 0;
-        if (g < N) shell_interval(tp, shell[g], t0, inv_dt, T, bpr, n_ranges, lo[j], hi[j]);
+        if (g < N) shell_bins(tp, shell[g], t0, inv_dt, T, lo[j], hi[j]);
     }
 #pragma unroll
     for (int j = 0; j < BIN_GPT; ++j)
-        for (int r = 0; r < n_ranges; ++r) {
-            unsigned b = __ballot_sync(0xffffffffu, lo[j] <= r && r <= hi[j]);
+        for (int r = 0; r < n_buckets; ++r) {
+            unsigned b = __ballot_sync(0xffffffffu, entry_in_bucket(lo[j], hi[j], r, L, bucket) >= 0);
             if (lane == 0) wc[j][warp][r] = __popc(b);
         }
     __syncthreads();
-    if (threadIdx.x < n_ranges) {
+    if (threadIdx.x < n_buckets) {
         int r = threadIdx.x, run = 0;
         for (int j = 0; j < BIN_GPT; ++j)
             for (int w = 0; w < BIN_THREADS / 32; ++w) { int v = wc[j][w][r]; wc[j][w][r] = run; run += v; }
@@ -208,13 +209,13 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __
 #pragma unroll
     for (int j = 0; j < BIN_GPT; ++j) {
         int g = chunk * BIN_CHUNK + j * BIN_THREADS + threadIdx.x;
-        for (int r = 0; r < n_ranges; ++r) {
-            bool m = lo[j] <= r && r <= hi[j];
-            unsigned b = __ballot_sync(0xffffffffu, m);
-            if (m) {
-                size_t cell = (size_t)tile * n_ranges + r;
+        for (int r = 0; r < n_buckets; ++r) {
+            int e = entry_in_bucket(lo[j], hi[j], r, L, bucket);
+            unsigned b = __ballot_sync(0xffffffffu, e >= 0);
+            if (e >= 0) {
+                size_t cell = (size_t)tile * n_buckets + r;
                 long long pos = cell_offsets[cell] + chunk_off[cell * n_chunks + chunk] + wc[j][warp][r] + __popc(b & lt);
-                if (pos < capacity) list[pos] = g;
+                if (pos < capacity) list[pos] = (unsigned)g | ((unsigned)e << NLOS_ENTRY_SHIFT);
                 else header[2] = 1;
             }
         }
@@ -223,43 +224,54 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __
 
 extern "C" int nlosb200_bin_num_chunks(int N) { return (N + BIN_CHUNK - 1) / BIN_CHUNK; }
 
-extern "C" int nlosb200_bin_shells_plan(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                                        int bins_per_range, int slice_len, int warps_per_block, int* chunk_counts, int* cell_counts,
-                                        long long* cell_offsets, int* cell_sub_off, int* tile_items, long long* header, void* stream)
+static int check_window(const char* who, int T, int window, int bucket, int N)
 {
-    NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && bins_per_range > 0 && slice_len > 0 && warps_per_block > 0, "bin_shells_plan: bad sizes");
-    int n_ranges = (T + bins_per_range - 1) / bins_per_range;
-    NLOS_REQUIRE(n_ranges <= BIN_MAX_RANGES, "bin_shells_plan: %d ranges > %d (raise bins_per_range)", n_ranges, BIN_MAX_RANGES);
-    NLOS_REQUIRE(n_tiles <= 65535, "bin_shells_plan: n_tiles=%d > 65535 (shard the scan grid)", n_tiles);
-    NLOS_REQUIRE(tiles && shell && chunk_counts && cell_counts && cell_offsets && cell_sub_off && tile_items && header,
-                 "bin_shells_plan: null pointer");
+    NLOS_REQUIRE(window >= 32 && (window & (window - 1)) == 0, "%s: window=%d must be a power of two >= 32", who, window);
+    NLOS_REQUIRE(bucket >= 1 && 2 * bucket <= window, "%s: bucket=%d must be in [1, window/2]", who, bucket);
+    NLOS_REQUIRE((T + bucket - 1) / bucket <= BIN_MAX_RANGES, "%s: %d buckets > %d (raise the bucket size)", who, (T + bucket - 1) / bucket,
+                 BIN_MAX_RANGES);
+    NLOS_REQUIRE(N < (1 << NLOS_ENTRY_SHIFT), "%s: N=%d >= 2^%d", who, N, NLOS_ENTRY_SHIFT);
+    NLOS_REQUIRE((T + (window - bucket) - 1) / (window - bucket) < (1 << (32 - NLOS_ENTRY_SHIFT)), "%s: too many sub-intervals", who);
+    return 0;
+}
+
+extern "C" int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
+                                        int window, int bucket, int slice_len, int warps_per_block, int* chunk_counts, int* cell_counts,
+                                        long long* cell_offsets, int* tile_items, long long* header, void* stream)
+{
+    NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && slice_len > 0 && warps_per_block > 0, "bin_window_plan: bad sizes");
+    int rc = check_window("bin_window_plan", T, window, bucket, N);
+    if (rc) return rc;
+    int n_buckets = (T + bucket - 1) / bucket;
+    NLOS_REQUIRE(n_tiles <= 65535, "bin_window_plan: n_tiles=%d > 65535 (shard the scan grid)", n_tiles);
+    NLOS_REQUIRE(tiles && shell && chunk_counts && cell_counts && cell_offsets && tile_items && header, "bin_window_plan: null pointer");
     int n_chunks = (N + BIN_CHUNK - 1) / BIN_CHUNK;
     float inv_dt = 1.0f / dt;
     cudaStream_t s = (cudaStream_t)stream;
     shell_count_kernel<<<dim3(n_chunks, n_tiles), BIN_THREADS, 0, s>>>(tiles, A, reinterpret_cast<const float4*>(shell), N, t0, inv_dt, T,
-                                                                       bins_per_range, n_ranges, n_chunks, chunk_counts);
+                                                                       window - bucket, bucket, n_buckets, n_chunks, chunk_counts);
     NLOS_CHECK_LAUNCH("shell_count_kernel");
-    scan_chunks_kernel<<<n_tiles * n_ranges, 256, 0, s>>>(chunk_counts, n_chunks, cell_counts);
+    scan_chunks_kernel<<<n_tiles * n_buckets, 256, 0, s>>>(chunk_counts, n_chunks, cell_counts);
     NLOS_CHECK_LAUNCH("scan_chunks_kernel");
-    scan_cells_kernel<<<1, 1024, 0, s>>>(cell_counts, n_tiles, n_ranges, slice_len, warps_per_block, cell_offsets, cell_sub_off, tile_items,
-                                         header);
+    scan_cells_kernel<<<1, 1024, 0, s>>>(cell_counts, n_tiles, n_buckets, slice_len, warps_per_block, cell_offsets, tile_items, header);
     NLOS_CHECK_LAUNCH("scan_cells_kernel");
     return 0;
 }
 
-extern "C" int nlosb200_bin_shells_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                                        int bins_per_range, const int* chunk_counts_scanned, const long long* cell_offsets, int* list,
+extern "C" int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
+                                        int window, int bucket, const int* chunk_counts_scanned, const long long* cell_offsets, int* list,
                                         long long list_capacity, long long* header, void* stream)
 {
-    NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && bins_per_range > 0, "bin_shells_fill: bad sizes");
-    int n_ranges = (T + bins_per_range - 1) / bins_per_range;
-    NLOS_REQUIRE(n_ranges <= BIN_MAX_RANGES, "bin_shells_fill: too many ranges");
-    NLOS_REQUIRE(list || list_capacity == 0, "bin_shells_fill: null list");
+    NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0, "bin_window_fill: bad sizes");
+    int rc = check_window("bin_window_fill", T, window, bucket, N);
+    if (rc) return rc;
+    int n_buckets = (T + bucket - 1) / bucket;
+    NLOS_REQUIRE(list || list_capacity == 0, "bin_window_fill: null list");
     int n_chunks = (N + BIN_CHUNK - 1) / BIN_CHUNK;
     float inv_dt = 1.0f / dt;
     shell_fill_kernel<<<dim3(n_chunks, n_tiles), BIN_THREADS, 0, (cudaStream_t)stream>>>(
-        tiles, A, reinterpret_cast<const float4*>(shell), N, t0, inv_dt, T, bins_per_range, n_ranges, n_chunks, chunk_counts_scanned,
-        cell_offsets, list, list_capacity, header);
+        tiles, A, reinterpret_cast<const float4*>(shell), N, t0, inv_dt, T, window - bucket, bucket, n_buckets, n_chunks, chunk_counts_scanned,
+        cell_offsets, reinterpret_cast<unsigned*>(list), list_capacity, header);
     NLOS_CHECK_LAUNCH("shell_fill_kernel");
     return 0;
 }

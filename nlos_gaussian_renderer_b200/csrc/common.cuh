@@ -16,6 +16,7 @@
 #define NLOS_TILE 32          // scan points per tile == lanes per warp
 #define NLOS_NTAB 7           // per-tile lattice tables
 #define NLOS_PINFO_ROWS 12
+#define NLOS_ENTRY_SHIFT 26   // list entry = gaussian id | (sub-interval index << 26)
 
 // record layout (float index)
 #define REC_MU 0      // 0..2 mean

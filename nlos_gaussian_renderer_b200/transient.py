@@ -14,7 +14,7 @@ from . import _lib
 from .geometry import ScanGeometry, TILE
 
 MODES = {"numerical": 0, "analytic": 1, "analytic_exact": 1}
-N_WARP_SLOTS = 148 * 16      # B200: 148 SMs x 2 CTAs x 8 warps
+N_SM = 148                    # B200
 
 
 def _f32c(t):
@@ -25,13 +25,21 @@ def _f32c(t):
 class TransientRenderer:
     """Stateful renderer for one ScanGeometry: owns the preprocess / binning workspaces."""
 
-    def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", bins_per_range=64, slice_len=None,
+    def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=128, bucket=None, slice_len=None,
                  mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0):
+        """window: bins of the per-warp sliding accumulator (power of two); bucket: bins the window advances by
+        (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries per warp (default: sized so that
+        the grid is a few waves of the 148 SMs)."""
         self.geom = geom
         self.T, self.t0, self.dt, self.c_deltaT = int(T), float(t0), float(dt), float(c_deltaT)
         self.mode = MODES[mode] if isinstance(mode, str) else int(mode)
-        self.bpr = int(min(bins_per_range, max(self.T, 1)))
-        self.n_ranges = -(-self.T // self.bpr)
+        self.window = int(window)
+        if bucket is None:
+            bucket = 8
+            while -(-self.T // bucket) > 64:
+                bucket *= 2
+        self.bucket = int(bucket)
+        self.n_buckets = -(-self.T // self.bucket)
         self.slice_len = slice_len
         self.mcut, self.mod, self.sigma = float(mcut), float(scaling_modifier), float(sigma_bbox)
         self.wpb = _lib.lib().nlosb200_transient_warps_per_block()
@@ -45,7 +53,7 @@ class TransientRenderer:
         if self._N == N:
             return
         L = _lib.lib()
-        n_cells = self.geom.n_tiles * self.n_ranges
+        n_cells = self.geom.n_tiles * self.n_buckets
         self.records = torch.empty(N * L.nlosb200_record_floats() + 32, dtype=torch.float32, device=dev)
         off = ((-self.records.data_ptr()) % 128) // 4         # 128-byte alignment for the TMA gather
         self.records = self.records[off: off + N * L.nlosb200_record_floats()]
@@ -53,20 +61,19 @@ class TransientRenderer:
         self.chunk_counts = torch.empty(n_cells * L.nlosb200_bin_num_chunks(N), dtype=torch.int32, device=dev)
         self.cell_counts = torch.empty(n_cells, dtype=torch.int32, device=dev)
         self.cell_offsets = torch.empty(n_cells + 1, dtype=torch.int64, device=dev)
-        self.cell_sub_off = torch.empty(n_cells, dtype=torch.int32, device=dev)
         self.tile_items = torch.empty(self.geom.n_tiles + 1, dtype=torch.int32, device=dev)
         self.header = torch.zeros(4, dtype=torch.int64, device=dev)
         self.dacc = torch.empty(N, L.nlosb200_grad_floats(), dtype=torch.float32, device=dev)
         self._N = N
         if self.slice_len is None:
-            est = self.geom.n_tiles * N * 2.5
-            self._slice = int(min(512, max(16, est / (N_WARP_SLOTS * 6)))) // 4 * 4
+            est = self.geom.n_tiles * N * 1.05                    # ~one entry per (tile, Gaussian)
+            self._slice = int(min(1024, max(16, est / (N_SM * self.wpb * 8)))) // 4 * 4      # ~8 waves of one CTA per SM
         else:
             self._slice = int(self.slice_len)
 
     def _bin_args(self):
         g = self.geom
-        return (g.tiles().data_ptr(), g.n_tiles, g.A, self.shell.data_ptr(), self._N, self.t0, self.dt, self.T, self.bpr)
+        return (g.tiles().data_ptr(), g.n_tiles, g.A, self.shell.data_ptr(), self._N, self.t0, self.dt, self.T, self.window, self.bucket)
 
     def prepare(self, means, log_scales, rotations, opacities, features):
         """preprocess + shell binning for the current parameters (stream ordered; ONE 16-byte readback
@@ -81,22 +88,21 @@ class TransientRenderer:
         _lib.call("nlosb200_preprocess", means.data_ptr(), log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(),
                   features.data_ptr(), N, features.shape[1], self.mod, self.sigma, self.mcut, self.records.data_ptr(),
                   self.shell.data_ptr(), None, st)
-        _lib.call("nlosb200_bin_shells_plan", *self._bin_args(), self._slice, self.wpb, self.chunk_counts.data_ptr(),
-                  self.cell_counts.data_ptr(), self.cell_offsets.data_ptr(), self.cell_sub_off.data_ptr(),
-                  self.tile_items.data_ptr(), self.header.data_ptr(), st)
+        _lib.call("nlosb200_bin_window_plan", *self._bin_args(), self._slice, self.wpb, self.chunk_counts.data_ptr(),
+                  self.cell_counts.data_ptr(), self.cell_offsets.data_ptr(), self.tile_items.data_ptr(), self.header.data_ptr(), st)
         hdr = self.header.cpu()
         total, self.n_items = int(hdr[0]), int(hdr[1])
         self.last_total = total
         if self._list is None or self._list.numel() < total:
             self._list = torch.empty(max(int(total * 1.25), 1024), dtype=torch.int32, device=means.device)
-        _lib.call("nlosb200_bin_shells_fill", *self._bin_args(), self.chunk_counts.data_ptr(), self.cell_offsets.data_ptr(),
+        _lib.call("nlosb200_bin_window_fill", *self._bin_args(), self.chunk_counts.data_ptr(), self.cell_offsets.data_ptr(),
                   self._list.data_ptr(), self._list.numel(), self.header.data_ptr(), st)
 
     def _render_args(self):
         g = self.geom
         return (g.tiles().data_ptr(), g.n_tiles, g.A, self.records.data_ptr(), self._N, self._list.data_ptr(),
-                self.cell_offsets.data_ptr(), self.cell_counts.data_ptr(), self.cell_sub_off.data_ptr(), self.tile_items.data_ptr(),
-                self.n_items, self.t0, self.dt, self.T, self.bpr, self._slice)
+                self.cell_offsets.data_ptr(), self.tile_items.data_ptr(), self.n_items, self.t0, self.dt, self.T, self.window, self.bucket,
+                self._slice)
 
     def forward_tiled(self):
         """-> H [n_tiles*32, T] in tile-major scan order (after prepare())."""
@@ -139,7 +145,8 @@ class TransientRenderer:
     def lists(self):
         """(cell_counts, cell_offsets, list) as CPU numpy arrays -- for the bit-exact binning tests."""
         total = self.last_total
-        return (self.cell_counts.cpu().numpy(), self.cell_offsets.cpu().numpy(), self._list[:total].cpu().numpy())
+        import numpy as np
+        return (self.cell_counts.cpu().numpy(), self.cell_offsets.cpu().numpy(), self._list[:total].cpu().numpy().view(np.uint32))
 
 
 class _TransientFn(torch.autograd.Function):

@@ -178,6 +178,51 @@ def shell_lists(lo, hi, n_ranges):
     return counts, offsets, lst
 
 
+def shell_bins(scan_o, Sy, Sx, tile_y, tile_x, means, log_scales, scaling_modifier, mcut, t0, dt, T, exp_mode=1):
+    """Tile-level shell of every Gaussian in bin units -> (klo, khi) int32 [n_tiles, N]; klo > khi = empty."""
+    scan_o, means, log_scales = _f(scan_o).reshape(-1, 3), _f(means), _f(log_scales)
+    N = means.shape[0]
+    nt = ((Sy + tile_y - 1) // tile_y) * ((Sx + tile_x - 1) // tile_x)
+    lo = np.empty((nt, N), np.int32)
+    hi = np.empty((nt, N), np.int32)
+    lib().orc_shell_bins(_p(scan_o), C.c_int(Sy), C.c_int(Sx), C.c_int(tile_y), C.c_int(tile_x), _p(means), _p(log_scales),
+                         C.c_int(N), C.c_float(scaling_modifier), C.c_float(mcut), C.c_int(exp_mode), C.c_float(t0), C.c_float(dt),
+                         C.c_int(T), _p(lo), _p(hi))
+    return lo, hi
+
+
+ENTRY_SHIFT = 26      # list entry = gaussian id | (sub-interval index << 26)
+
+
+def window_lists(klo, khi, T, window, bucket):
+    """DEFINITION of the window-binning lists the batched renderer consumes.  A Gaussian whose tile-level shell is
+    [klo, khi] contributes entries e = 0 .. ceil(len/L)-1 with L = window - bucket; entry e covers bins
+    [klo + e L, min(khi, klo + (e+1) L - 1)] and lives in cell (tile, (klo + e L) // bucket).  Per cell the entries are
+    ascending in the Gaussian id.  -> counts [n_tiles*n_buckets] int32, offsets int64 [cells+1], list uint32."""
+    klo = np.asarray(klo, np.int64)
+    khi = np.asarray(khi, np.int64)
+    nt, N = klo.shape
+    L = window - bucket
+    nb = -(-T // bucket)
+    n_e = np.where(klo <= khi, -(-(khi - klo + 1) // L), 0)
+    cells, vals = [], []
+    for e in range(int(n_e.max()) if n_e.size else 0):
+        t, g = np.nonzero(n_e > e)
+        s = klo[t, g] + e * L
+        cells.append(t * nb + s // bucket)
+        vals.append(g | (e << ENTRY_SHIFT))
+    if cells:
+        cells, vals = np.concatenate(cells), np.concatenate(vals)
+        order = np.lexsort((vals & ((1 << ENTRY_SHIFT) - 1), cells))
+        cells, vals = cells[order], vals[order]
+    else:
+        cells, vals = np.zeros(0, np.int64), np.zeros(0, np.int64)
+    counts = np.bincount(cells, minlength=nt * nb).astype(np.int32)
+    offsets = np.zeros(nt * nb + 1, np.int64)
+    np.cumsum(counts, out=offsets[1:])
+    return counts, offsets, vals.astype(np.uint32)
+
+
 def knn_dist2(points):
     points = _f(points).reshape(-1, 3)
     out = np.empty(points.shape[0], np.float32)

@@ -20,22 +20,26 @@ def _renderer(geom, ta, mode, **kw):
     return TransientRenderer(geom, ta["t_samples"].numel(), ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, **kw)
 
 
-@pytest.mark.parametrize("shape", [(150, 5, 9, 48, 6), (1000, 16, 16, 128, 8), (400, 8, 8, 200, 8)])
-@pytest.mark.parametrize("bpr", [64, 32])
-def test_shell_lists_bit_exact(shape, bpr):
+@pytest.mark.parametrize("shape,scale_mul", [((150, 5, 9, 48, 6), 1.0), ((1000, 16, 16, 128, 8), 1.0), ((400, 8, 8, 200, 8), 1.0),
+                                             ((300, 6, 10, 512, 6), 6.0)])
+@pytest.mark.parametrize("window,bucket", [(128, 8), (32, 8), (64, 16)])
+def test_window_lists_bit_exact(shape, scale_mul, window, bucket):
+    """cell counts / offsets / entry lists of the window binning == the oracle's definition (oracle.window_lists), bit for bit;
+    small windows and large Gaussians exercise the split entries (e > 0)."""
     N, Sy, Sx, T, A = shape
-    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, device="cuda")
-    r = _renderer(geom, ta, "numerical", bins_per_range=bpr)
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=scale_mul, device="cuda")
+    r = _renderer(geom, ta, "numerical", window=window, bucket=bucket)
     r.prepare(*params)
     cnt, off, lst = r.lists()
-    lo, hi = oracle.shell_intervals(util.np32(geom.scan_o), Sy, Sx, geom.tile_y, geom.tile_x, util.np32(params[0]), util.np32(params[1]),
-                                    1.0, 5.3, ta["t0"], ta["dt"], T, bpr, exp_mode=1)
-    n_ranges = -(-T // bpr)
-    ocnt, ooff, olst = oracle.shell_lists(lo, hi, n_ranges)
+    klo, khi = oracle.shell_bins(util.np32(geom.scan_o), Sy, Sx, geom.tile_y, geom.tile_x, util.np32(params[0]), util.np32(params[1]),
+                                 1.0, 5.3, ta["t0"], ta["dt"], T, exp_mode=1)
+    ocnt, ooff, olst = oracle.window_lists(klo, khi, T, window, bucket)
     assert np.array_equal(cnt, ocnt)
     assert np.array_equal(off, ooff)
     assert np.array_equal(lst, olst)
     assert lst.size > 0
+    if window == 32 and scale_mul > 1:
+        assert (lst >> oracle.ENTRY_SHIFT).max() > 0          # split entries present
 
 
 @pytest.mark.parametrize("mode", ["numerical", "analytic"])
@@ -59,10 +63,12 @@ def test_forward_matches_oracle(mode, shape, scale_mul):
 
 def test_forward_slice_and_range_invariance():
     geom, ta, params = util.small_scene(600, 8, 8, 96, 6, device="cuda")
-    ref = _renderer(geom, ta, "numerical", bins_per_range=96, slice_len=4096).forward(*params)
-    for bpr, sl in [(16, 8), (32, 64), (64, 16)]:
-        H = _renderer(geom, ta, "numerical", bins_per_range=bpr, slice_len=sl).forward(*params)
-        assert util.rel_to_max(H.cpu().numpy(), ref.cpu().numpy()) < 2e-6
+    ref = _renderer(geom, ta, "numerical", window=128, bucket=8, slice_len=4096).forward(*params)
+    for win, bk, sl in [(32, 8, 8), (64, 16, 64), (128, 32, 16), (64, 8, 4)]:
+        H = _renderer(geom, ta, "numerical", window=win, bucket=bk, slice_len=sl).forward(*params)
+        # chunks evaluate the union of their rays' cut intervals, clipped to the entry's sub-interval: the tails beyond the
+        # 5.3-sigma cut (<= 1e-6 of a Gaussian's peak) differ between decompositions
+        assert util.rel_to_max(H.cpu().numpy(), ref.cpu().numpy()) < 5e-6
 
 
 @pytest.mark.parametrize("mode", ["numerical", "analytic"])
@@ -90,6 +96,27 @@ def test_backward_matches_autograd(mode):
         e = util.rel_to_max(a.grad.cpu().numpy(), b.grad.numpy())
         print(f"{mode} grad {name}: rel-to-max err {e:.2e}  (max |g| {b.grad.abs().max():.3e})")
         assert e < TOL, name
+
+
+@pytest.mark.parametrize("mode", ["numerical", "analytic"])
+def test_split_entries_forward_backward(mode):
+    """window=32: Gaussians longer than L=24 bins are rendered through several entries (sub-intervals); forward must still match the
+    oracle and the gradients must equal those of the unsplit decomposition."""
+    N, Sy, Sx, T, A = 200, 5, 9, 160, 6
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=3.0, device="cuda")
+    gH = torch.rand(Sy, Sx, T, generator=torch.Generator().manual_seed(1)).cuda()
+    outs = []
+    for win, bk in ((32, 8), (128, 8)):
+        r = _renderer(geom, ta, mode, window=win, bucket=bk, slice_len=16)
+        ps = [p.clone().requires_grad_() for p in params]
+        H = render_transient_batch(r, *ps)
+        (H * gH).sum().backward()
+        outs.append((H.detach().cpu().numpy(), [p.grad.cpu().numpy() for p in ps], r))
+    assert (outs[0][2].lists()[2] >> oracle.ENTRY_SHIFT).max() > 0
+    H64 = util.oracle_H(geom, ta, params, mode=0 if mode == "numerical" else 1, precision="f64")
+    assert util.rel_to_max(outs[0][0].reshape(-1, T), H64) < TOL
+    for a, b in zip(outs[0][1], outs[1][1]):
+        assert util.rel_to_max(a, b) < 2e-5
 
 
 def scenes_cpu(geom):
