@@ -51,7 +51,7 @@ int nlosb200_build_scan_tiles(const float* scan_o, const float* sin_th, const fl
 
 /* ---- window binning (replaces filter_gaussians_kernel, src/ray_aabb.cu:10-102, as the culling structure of the batched
  * renderer).  Per (tile, Gaussian) the conservative radial shell is an inclusive bin interval [klo,khi]; the renderer's
- * accumulator is a sliding window of `window` bins (power of two) advancing in steps of `bucket` bins, so a Gaussian is
+ * accumulator is a sliding window of `window` bins (multiple of 8) advancing in steps of `bucket` bins, so a Gaussian is
  * listed once per tile unless its interval is longer than L = window-bucket (then entry e covers [klo+eL, klo+(e+1)L-1]).
  * Entry (g,e) lives in cell (tile, (klo+eL)/bucket); list value = g | e<<26; per cell ascending g.
  * n_buckets = ceil(T/bucket) <= 64, n_cells = n_tiles*n_buckets.

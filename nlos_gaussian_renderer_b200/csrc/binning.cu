@@ -226,7 +226,7 @@ extern "C" int nlosb200_bin_num_chunks(int N) { return (N + BIN_CHUNK - 1) / BIN
 
 static int check_window(const char* who, int T, int window, int bucket, int N)
 {
-    NLOS_REQUIRE(window >= 32 && (window & (window - 1)) == 0, "%s: window=%d must be a power of two >= 32", who, window);
+    NLOS_REQUIRE(window >= 32 && window % 8 == 0, "%s: window=%d must be a multiple of 8, >= 32", who, window);
     NLOS_REQUIRE(bucket >= 1 && 2 * bucket <= window, "%s: bucket=%d must be in [1, window/2]", who, bucket);
     NLOS_REQUIRE((T + bucket - 1) / bucket <= BIN_MAX_RANGES, "%s: %d buckets > %d (raise the bucket size)", who, (T + bucket - 1) / bucket,
                  BIN_MAX_RANGES);

@@ -10,7 +10,7 @@
 //   CTA  = one scan tile (32 scan points) ; its lattice tables arrive with ONE TMA bulk copy
 //   warp = one slice of the tile's entry list (binning.cu: entries ordered by the first bin of the Gaussian's shell)
 //   lane = scan point.  Each warp owns a private SLIDING WINDOW accumulator [window bins][32] in shared memory
-//   (ring indexed by bin & (window-1), bank == lane -> conflict-free read-modify-write without atomics) that
+//   (ring indexed by bin mod window, bank == lane -> conflict-free read-modify-write without atomics) that
 //   advances with the list: bins that fall behind are flushed with coalesced float REDs (forward) or refilled with
 //   the incoming dL/dH weights (backward).  A Gaussian is therefore set up ONCE per (tile, scan point) however many
 //   bins it covers.  Records are gathered with per-record TMA bulk copies through a 2-stage mbarrier ring.
@@ -21,7 +21,8 @@
 //   2. hits are consumed RC at a time ("chunk"): centred quadratic m2(r) = m2min + C (r - r*)^2, bin interval of
 //      the 5.3-sigma cut; ONE loop over the union of the chunk's bin intervals in which every ray advances
 //      e_{k+1} = e_k g_k,  g_{k+1} = g_k q  (a Gaussian on a uniform grid is a second-order geometric recurrence,
-//      q = exp(-C dt^2)), re-seeded with MUFU.EX2 every TR_SEG bins: 2 FMUL + 1 FADD per sample-eval and ONE
+//      q = exp(-C dt^2)), re-seeded with MUFU.EX2 every TR_SEG bins, evaluated two rays at a time with the packed
+//      fp32x2 instructions of sm_100 (FMUL2/FADD2/FFMA2): 1.5 issue slots per sample-eval and ONE
 //      shared-memory read-modify-write per (chunk, bin).  Rays the recurrence cannot carry (seed underflow,
 //      Gaussians much narrower than a bin) take a direct 1-MUFU-per-bin path;
 //   3. backward: per ray three moments sum_k w_k e_k k^n (n = 0,1,2) in registers, chain rule to dL/dM, dL/dmu,
@@ -31,7 +32,7 @@
 
 using namespace nlos;
 
-#define TR_WPB 8           // warps per CTA
+#define TR_WPB 12          // warps per CTA
 #define TR_MINB 1          // CTAs per SM the register allocation is sized for
 #define TR_RING 4          // records per ring stage
 #define TR_STAGES 2
@@ -94,7 +95,9 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
     constexpr int RC = ChunkWidth<MODE, BWD>::value;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int A = P.A;
-    const int W = P.window, Wm = P.window - 1, BS = P.bucket, L = P.window - P.bucket;
+    const int W = P.window, BS = P.bucket, L = P.window - P.bucket;
+    const unsigned wmagic = 0xFFFFFFFFu / (unsigned)P.window + 1u;
+    auto wrap = [&](int k) { return k - (int)__umulhi((unsigned)k, wmagic) * W; };      // k mod window for 0 <= k < 2^20
     const int tile_floats = (NLOS_NTAB * A + NLOS_PINFO_ROWS) * NLOS_TILE;
     float* s_tab = reinterpret_cast<float*>(smem_raw);
     float* s_pi = s_tab + NLOS_NTAB * A * NLOS_TILE;
@@ -157,7 +160,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
     auto flush = [&](int k_from, int cnt) {          // forward: H[p,k] += acc * hscale_p / (r_k^2 + 1e-8) * flush_scale  (cuda_autograd.py:308-314)
         for (int idx = lane; idx < cnt * NLOS_TILE; idx += 32) {
             const int pp = idx / cnt, k = k_from + (idx - pp * cnt);
-            float* slot = Hw + (k & Wm) * NLOS_TILE + pp;
+            float* slot = Hw + wrap(k) * NLOS_TILE + pp;
             const float v = *slot;
             *slot = 0.f;
             if (v != 0.f && k < T) {
@@ -174,7 +177,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                 const float rk = fmaf((float)k, dt, t0);
                 v = P.gH[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (rk * rk + 1e-8f);
             }
-            Hw[(k & Wm) * NLOS_TILE + pp] = v;
+            Hw[wrap(k) * NLOS_TILE + pp] = v;
         }
     };
     int base = -0x40000000;                           // "no window yet"
@@ -370,10 +373,12 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                 const float kfc = 0.5f * (kmaxf - kminf);                    // moments are taken about the middle of the chunk's bins
                                 if (anyfast) {
                                     float kf = -kfc;
+                                    const f32x2 q01 = pack2(qq[0], qq[1]), q23 = pack2(qq[2], qq[3]);
+                                    f32x2 A01 = 0ull, A23 = 0ull, B01 = 0ull, B23 = 0ull, C01 = 0ull, C23 = 0ull;     // packed moments
                                     for (int ks = kmin; ks <= kmax;) {
-                                        const int nseg = min(min(TR_SEG, kmax - ks + 1), W - (ks & Wm));      // never across the ring's wrap
+                                        const int nseg = min(min(TR_SEG, kmax - ks + 1), W - wrap(ks));      // never across the ring's wrap
                                         const float tks = fmaf((float)ks, dt, t0);
-                                        float* hp = Hw + (ks & Wm) * NLOS_TILE + lane;
+                                        float* hp = Hw + wrap(ks) * NLOS_TILE + lane;
 #pragma unroll
                                         for (int u = 0; u < RC; ++u) {
                                             const float tu = tks - rs[u];
@@ -383,33 +388,41 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                             e[u] = fr[u] ? (BWD ? ev : wt[u] * ev) : 0.f;
                                             g[u] = fr[u] ? gv : 0.f;
                                         }
+                                        // packed fp32x2: rays (0,1) and (2,3) share one FMUL2 / FADD2 / FFMA2 each
+                                        f32x2 e01 = pack2(e[0], e[1]), e23 = pack2(e[2], e[3]);
+                                        f32x2 g01 = pack2(g[0], g[1]), g23 = pack2(g[2], g[3]);
                                         if (!BWD) {
 #pragma unroll 4
                                             for (int kk = 0; kk < nseg; ++kk) {
-                                                float acc = 0.f;
-#pragma unroll
-                                                for (int u = 0; u < RC; ++u) { acc += e[u]; e[u] *= g[u]; g[u] *= qq[u]; }
-                                                *hp += acc;
+                                                float lo, hi;
+                                                unpack2(add2(e01, e23), lo, hi);
+                                                e01 = mul2(e01, g01); e23 = mul2(e23, g23);
+                                                g01 = mul2(g01, q01); g23 = mul2(g23, q23);
+                                                *hp += lo + hi;
                                                 hp += NLOS_TILE;
                                             }
                                         } else {
 #pragma unroll 2
                                             for (int kk = 0; kk < nseg; ++kk) {
                                                 const float w = *hp;
-#pragma unroll
-                                                for (int u = 0; u < RC; ++u) {
-                                                    const float we = w * e[u], wk = we * kf;
-                                                    S0[u] += we;
-                                                    S1[u] += wk;
-                                                    S2[u] = fmaf(wk, kf, S2[u]);
-                                                    e[u] *= g[u];
-                                                    g[u] *= qq[u];
-                                                }
+                                                const f32x2 w2 = pack2(w, w), k2 = pack2(kf, kf);
+                                                const f32x2 we01 = mul2(w2, e01), we23 = mul2(w2, e23);
+                                                const f32x2 wk01 = mul2(we01, k2), wk23 = mul2(we23, k2);
+                                                A01 = add2(A01, we01); A23 = add2(A23, we23);
+                                                B01 = add2(B01, wk01); B23 = add2(B23, wk23);
+                                                C01 = fma2(wk01, k2, C01); C23 = fma2(wk23, k2, C23);
+                                                e01 = mul2(e01, g01); e23 = mul2(e23, g23);
+                                                g01 = mul2(g01, q01); g23 = mul2(g23, q23);
                                                 kf += 1.0f;
                                                 hp += NLOS_TILE;
                                             }
                                         }
                                         ks += nseg;
+                                    }
+                                    if (BWD) {
+                                        unpack2(A01, S0[0], S0[1]); unpack2(A23, S0[2], S0[3]);
+                                        unpack2(B01, S1[0], S1[1]); unpack2(B23, S1[2], S1[3]);
+                                        unpack2(C01, S2[0], S2[1]); unpack2(C23, S2[2], S2[3]);
                                     }
                                 }
                                 if (BWD) {
@@ -432,7 +445,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         float t = fmaf((float)klo, dt, t0) - rs[u];
                                         float a0 = 0.f, a1 = 0.f, a2 = 0.f;
                                         for (int k = klo; k <= khi; ++k) {
-                                            float* hp = Hw + (k & Wm) * NLOS_TILE + lane;
+                                            float* hp = Hw + wrap(k) * NLOS_TILE + lane;
                                             const float ev = ex2_approx(fmaf(gam[u], t * t, al[u]));
                                             if (!BWD) {
                                                 *hp = fmaf(wt[u], ev, *hp);
@@ -501,12 +514,12 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                                 acc = fmaf(wt[u] * pref[u], E - Ep[u], acc);
                                                 Ep[u] = E;
                                             }
-                                            Hw[(k & Wm) * NLOS_TILE + lane] += acc;
+                                            Hw[wrap(k) * NLOS_TILE + lane] += acc;
                                             kf += 1.0f;
                                         }
                                     } else {
                                         for (int k = kmin; k <= kmax; ++k) {
-                                            const float w = Hw[(k & Wm) * NLOS_TILE + lane];
+                                            const float w = Hw[wrap(k) * NLOS_TILE + lane];
 #pragma unroll
                                             for (int u = 0; u < RC; ++u) {
                                                 const float uu = fmaf(kf, dt, u0[u]);
@@ -630,7 +643,7 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
                        float c_deltaT, float mcut, int mode)
 {
     NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && A >= 1 && A <= 128, "transient: bad sizes");
-    NLOS_REQUIRE(window >= 32 && (window & (window - 1)) == 0 && bucket >= 1 && 2 * bucket <= window && slice_len > 0,
+    NLOS_REQUIRE(window >= 32 && window % 8 == 0 && bucket >= 1 && 2 * bucket <= window && slice_len > 0,
                  "transient: bad window/bucket/slice_len");
     NLOS_REQUIRE(mode == MODE_NUM || mode == MODE_ANA, "transient: mode must be 0 (numerical) or 1 (analytic-exact)");
     NLOS_REQUIRE(tiles && records && list && cell_offsets && tile_items, "transient: null pointer");

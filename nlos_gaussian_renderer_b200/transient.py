@@ -25,9 +25,9 @@ def _f32c(t):
 class TransientRenderer:
     """Stateful renderer for one ScanGeometry: owns the preprocess / binning workspaces."""
 
-    def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=128, bucket=None, slice_len=None,
+    def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
                  mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0):
-        """window: bins of the per-warp sliding accumulator (power of two); bucket: bins the window advances by
+        """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
         (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries per warp (default: sized so that
         the grid is a few waves of the 148 SMs)."""
         self.geom = geom
