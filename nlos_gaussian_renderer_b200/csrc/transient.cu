@@ -9,24 +9,27 @@
 // Work decomposition (B200: 148 SMs, one CTA of TR_WPB warps per SM):
 //   CTA  = one scan tile (32 scan points) ; its lattice tables arrive with ONE TMA bulk copy
 //   warp = one slice of the tile's entry list (binning.cu: entries ordered by the first bin of the Gaussian's shell)
-//   lane = scan point.  Each warp owns a private SLIDING WINDOW accumulator [window bins][32] in shared memory
-//   (ring indexed by bin mod window, bank == lane -> conflict-free read-modify-write without atomics) that
-//   advances with the list: bins that fall behind are flushed with coalesced float REDs (forward) or refilled with
-//   the incoming dL/dH weights (backward).  A Gaussian is therefore set up ONCE per (tile, scan point) however many
-//   bins it covers.  Records are gathered with per-record TMA bulk copies through a 2-stage mbarrier ring.
+//   lane = scan point.  Each warp owns a private LINEAR WINDOW [window bins][32] in shared memory (bank == lane ->
+//   conflict-free without atomics) that slides with the list: bins that fall behind are flushed with coalesced float
+//   REDs (forward) or refilled with the incoming dL/dH weights (backward).  Records are gathered with per-record TMA
+//   bulk copies through a 2-stage mbarrier ring.
 //
-// Per (Gaussian, scan point):
+// Per (Gaussian, scan point)  -- "pair":
 //   1. conservative (theta,phi) footprint rectangle from the 3-sigma AABB; every candidate ray gets the exact slab
 //      test (same predicate as cuda_utils.cuh:97-121); hits are collected in a 32-bit mask per 4x8 block;
-//   2. hits are consumed RC at a time ("chunk"): centred quadratic m2(r) = m2min + C (r - r*)^2, bin interval of
-//      the 5.3-sigma cut; ONE loop over the union of the chunk's bin intervals in which every ray advances
-//      e_{k+1} = e_k g_k,  g_{k+1} = g_k q  (a Gaussian on a uniform grid is a second-order geometric recurrence,
-//      q = exp(-C dt^2)), re-seeded with MUFU.EX2 every TR_SEG bins, evaluated two rays at a time with the packed
-//      fp32x2 instructions of sm_100 (FMUL2/FADD2/FFMA2): 1.5 issue slots per sample-eval and ONE
-//      shared-memory read-modify-write per (chunk, bin).  Rays the recurrence cannot carry (seed underflow,
-//      Gaussians much narrower than a bin) take a direct 1-MUFU-per-bin path;
-//   3. backward: per ray three moments sum_k w_k e_k k^n (n = 0,1,2) in registers, chain rule to dL/dM, dL/dmu,
-//      dL/dop, dL/dalb per lane, ONE warp-shuffle reduction per entry, 14 float REDs.
+//   2. every hit ray is a Gaussian in r on the uniform bin grid:  e_k = exp2(al + gam (t_k - r*)^2).  It is evaluated
+//      CENTRE-OUT from the pair's centre bin kc with the second-order geometric recurrence  e <- e g ; g <- g q
+//      (q = exp2(2 gam dt^2)), the UP direction (bins kc, kc+1, ..) and the DOWN direction (kc-1, kc-2, ..) packed in
+//      the two halves of one fp32x2 register (FMUL2/FADD2 of sm_100): 3 packed instructions per 2 sample-evals, 4 MUFU
+//      per ray, and -- because the seed sits at the peak -- errors are relative to values that only shrink;
+//   3. forward: the pair's bins live in REGISTERS (ACC[s] = {bin kc+s, bin kc-1-s}, static indices by full unrolling),
+//      summed over all rays of the pair and merged into the shared window ONCE per pair;
+//      backward: the three moments sum_k w_k e_k tau^n (n = 0,1,2) per ray from running prefix sums (A += w e; B += A;
+//      C += B), chain rule to dL/dM, dL/dmu, dL/dop, dL/dalb per lane, ONE warp-shuffle reduction per entry, 14 REDs;
+//   4. the analytic-exact mode integrates every bin with Gauss-Legendre nodes (2 or 4 by the ray's width in bins;
+//      <= 1e-5 of the peak, far below the 1e-4 parity tolerance): each node is one more recurrence stream on the same
+//      registers.  Rays narrower than 0.6 bins, or whose seeds are not representable, take the closed-form erf path
+//      (analytic) / the direct 1-MUFU-per-bin path (numerical).
 #include "common.cuh"
 #include "../../include/nlosb200.h"
 
@@ -36,9 +39,11 @@ using namespace nlos;
 #define TR_MINB 1          // CTAs per SM the register allocation is sized for
 #define TR_RING 4          // records per ring stage
 #define TR_STAGES 2
-#define TR_SEG 16          // bins between MUFU re-seeds of a recurrence
+#define TR_NH 32           // forward: register accumulators cover bins [kc - TR_NH, kc + TR_NH)
+#define TR_GUARD 4         // zero bins on either side of a warp's window (backward reads up to 3 bins past an entry)
 #define LOG2E_F 1.4426950408889634f
-#define TWO_OVER_SQRT_PI 1.1283791670955126f
+#define SQRT_PI_2 1.2533141373155001f
+#define NO_BASE (-0x40000000)
 
 enum { MODE_NUM = 0, MODE_ANA = 1, MODE_COUNT = 2 };
 
@@ -82,27 +87,49 @@ __device__ __forceinline__ float rsqrt_approx(float x)
     asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+__device__ __forceinline__ float lo_of(f32x2 v) { float a, b; unpack2(v, a, b); return a; }
+__device__ __forceinline__ float hi_of(f32x2 v) { float a, b; unpack2(v, a, b); return b; }
 
-template <int MODE, bool BWD>
-struct ChunkWidth {
-    static constexpr int value = (MODE == MODE_ANA && BWD) ? 2 : 4;     // rays per row chunk (register budget)
+// one hit ray of a pair: the Gaussian in r it restricts to (log2 domain) and its bin interval inside the entry
+struct RayQ {
+    float rs;      // r* : closest approach (Mahalanobis) along the ray
+    float gam;     // -0.5 log2(e) C          (C = |M d|^2)
+    float al;      // -0.5 log2(e) m2min
+    float sth;     // sin(theta) quadrature weight of the ray
+    float kl, kh;  // bins of the mcut cut clipped to the entry's sub-interval (kl > kh: nothing to do)
 };
 
+// moments of one packed {up, down} stream after n executed steps:  x_s = w e at step s,
+//   A = sum x,  B = sum_s A_s = sum x (n - s),  C = sum_s B_s = sum x (n-s)(n-s+1)/2
+// up bin kc+s has tau = tc + s dt, down bin kc-1-s has tau = tc - dt - s dt.
+__device__ __forceinline__ void stream_moments(f32x2 A, f32x2 B, f32x2 C, float nf, float tc, float dt, float& S0, float& S1, float& S2)
+{
+    float Au, Ad, Bu, Bd, Cu, Cd;
+    unpack2(A, Au, Ad); unpack2(B, Bu, Bd); unpack2(C, Cu, Cd);
+    const float M1u = fmaf(nf, Au, -Bu), M1d = fmaf(nf, Ad, -Bd);                                  // sum x s
+    const float M2u = fmaf(nf, fmaf(nf, Au, -2.0f * Bu), fmaf(2.0f, Cu, -Bu));                     // sum x s^2
+    const float M2d = fmaf(nf, fmaf(nf, Ad, -2.0f * Bd), fmaf(2.0f, Cd, -Bd));
+    const float td = tc - dt, dt2 = dt * dt;
+    S0 += Au + Ad;
+    S1 += fmaf(tc, Au, dt * M1u) + fmaf(td, Ad, -dt * M1d);
+    S2 += fmaf(tc * tc, Au, fmaf(2.0f * tc * dt, M1u, dt2 * M2u)) + fmaf(td * td, Ad, fmaf(-2.0f * td * dt, M1d, dt2 * M2d));
+}
 
 template <int MODE, bool BWD>
 __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const TransientParams P)
 {
-    constexpr int RC = ChunkWidth<MODE, BWD>::value;
+    constexpr bool FWD = !BWD && MODE != MODE_COUNT;
+    constexpr bool GRAD = BWD && MODE != MODE_COUNT;
+    constexpr int RC = (MODE == MODE_ANA) ? 1 : 2;          // hit rays consumed per iteration (analytic: one ray = 2 or 4 node streams)
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int A = P.A;
     const int W = P.window, BS = P.bucket, L = P.window - P.bucket;
-    const unsigned wmagic = 0xFFFFFFFFu / (unsigned)P.window + 1u;
-    auto wrap = [&](int k) { return k - (int)__umulhi((unsigned)k, wmagic) * W; };      // k mod window for 0 <= k < 2^20
     const int tile_floats = (NLOS_NTAB * A + NLOS_PINFO_ROWS) * NLOS_TILE;
+    const int wstride = (W + 2 * TR_GUARD) * NLOS_TILE;
     float* s_tab = reinterpret_cast<float*>(smem_raw);
     float* s_pi = s_tab + NLOS_NTAB * A * NLOS_TILE;
-    float* s_H = s_tab + tile_floats;                                   // [TR_WPB][window][32]
-    float* s_ring = s_H + TR_WPB * W * NLOS_TILE;                       // [TR_WPB][TR_STAGES][TR_RING][32]
+    float* s_H = s_tab + tile_floats;                                   // [TR_WPB][guard | window | guard][32]
+    float* s_ring = s_H + TR_WPB * wstride;                             // [TR_WPB][TR_STAGES][TR_RING][32]
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_ring + TR_WPB * TR_STAGES * TR_RING * NLOS_REC_FLOATS);   // [1 + TR_WPB*TR_STAGES]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -138,49 +165,62 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
     mbar_wait(&s_bar[0], 0);   // lattice tables + scan-point info have landed
     if (n == 0) return;
 
-    float* Hw = s_H + warp * W * NLOS_TILE;
+    float* Hw = s_H + warp * wstride + TR_GUARD * NLOS_TILE;            // bin `base` of this warp's window
     float* ring = s_ring + warp * TR_STAGES * TR_RING * NLOS_REC_FLOATS;
     uint64_t* bar = s_bar + 1 + warp * TR_STAGES;
 
     // ---- per-lane scan point
     const float ox = s_pi[PI_OX * 32 + lane], oy = s_pi[PI_OY * 32 + lane], oz = s_pi[PI_OZ * 32 + lane];
-    const float th0 = s_pi[PI_TH0 * 32 + lane], idth = s_pi[PI_IDTH * 32 + lane];
-    const float ph0 = s_pi[PI_PH0 * 32 + lane], idph = s_pi[PI_IDPH * 32 + lane];
     const int flags = __float_as_int(s_pi[PI_FLAGS * 32 + lane]);
     const bool valid = flags & 1, fast = flags & 2;
     const float t0 = P.t0, dt = P.dt, inv_dt = P.inv_dt, dt2 = P.dt * P.dt;
     const int T = P.T;
 
-    if (MODE != MODE_COUNT && !BWD)
-        for (int i = lane; i < W * NLOS_TILE; i += 32) Hw[i] = 0.f;
+    if (MODE != MODE_COUNT)
+        for (int i = lane; i < wstride; i += 32) Hw[i - TR_GUARD * NLOS_TILE] = 0.f;
     __syncwarp();
 
-    // ---- sliding window [base, base + W): flush (forward) / refill (backward) the bins that change when it advances
+    // ---- linear window [base, base + W): when it advances, the bins that fall behind are flushed (forward) and the
+    //      rest is shifted down; the backward pass refills the new bins with the weights dL/dH * hscale / (r^2+1e-8)
     const float* const s_hs = s_pi + PI_HSCALE * 32;
-    auto flush = [&](int k_from, int cnt) {          // forward: H[p,k] += acc * hscale_p / (r_k^2 + 1e-8) * flush_scale  (cuda_autograd.py:308-314)
+    int base = NO_BASE;
+    auto flush = [&](int cnt) {                       // forward: H[p,k] += acc * hscale_p / (r_k^2 + 1e-8) * flush_scale  (cuda_autograd.py:308-314)
         for (int idx = lane; idx < cnt * NLOS_TILE; idx += 32) {
-            const int pp = idx / cnt, k = k_from + (idx - pp * cnt);
-            float* slot = Hw + wrap(k) * NLOS_TILE + pp;
-            const float v = *slot;
-            *slot = 0.f;
+            const int pp = idx / cnt, kk = idx - pp * cnt, k = base + kk;
+            const float v = Hw[kk * NLOS_TILE + pp];
             if (v != 0.f && k < T) {
                 const float rk = fmaf((float)k, dt, t0);
                 atomicAdd(P.H + ((size_t)tile * NLOS_TILE + pp) * T + k, v * (s_hs[pp] * P.flush_scale) / (rk * rk + 1e-8f));
             }
         }
     };
-    auto refill = [&](int k_from, int cnt) {         // backward: W[k][p] = dL/dH[p,k] * hscale_p / (r_k^2 + 1e-8) * flush_scale
+    auto refill = [&](int nbase, int kk_from, int cnt) {       // backward: W[k][p] = dL/dH[p,k] * hscale_p / (r_k^2 + 1e-8) * flush_scale
         for (int idx = lane; idx < cnt * NLOS_TILE; idx += 32) {
-            const int pp = idx / cnt, k = k_from + (idx - pp * cnt);
+            const int pp = idx / cnt, kk = kk_from + (idx - pp * cnt), k = nbase + kk;
             float v = 0.f;
             if (k >= 0 && k < T) {
                 const float rk = fmaf((float)k, dt, t0);
                 v = P.gH[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (rk * rk + 1e-8f);
             }
-            Hw[wrap(k) * NLOS_TILE + pp] = v;
+            Hw[kk * NLOS_TILE + pp] = v;
         }
     };
-    int base = -0x40000000;                           // "no window yet"
+    auto advance = [&](int nbase) {
+        if (base == NO_BASE) {
+            if (BWD) refill(nbase, 0, W);
+        } else {
+            const int d = min(nbase - base, W);
+            if (!BWD) flush(d);
+            __syncwarp();
+            for (int k = 0; k < W - d; ++k) Hw[k * NLOS_TILE + lane] = Hw[(k + d) * NLOS_TILE + lane];
+            if (!BWD)
+                for (int k = W - d; k < W; ++k) Hw[k * NLOS_TILE + lane] = 0.f;
+            __syncwarp();
+            if (BWD) refill(nbase, W - d, d);
+        }
+        base = nbase;
+        __syncwarp();
+    };
     unsigned long long c_hits = 0, c_ws = 0, c_ev = 0, c_wb = 0;
 
     // ---- TMA ring over the list slice
@@ -217,6 +257,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
             const float cx = v0.x - ox, cy = v0.y - oy, cz = v0.z - oz;                             // mu - o
             // ---- the tile-level shell of this Gaussian, bit-identical to binning.cu:shell_bins (warp min/max over the scan points)
             int s_lo, s_hi;
+            bool split;
             float d2;
             {
                 d2 = __fadd_rn(__fadd_rn(__fmul_rn(cx, cx), __fmul_rn(cy, cy)), __fmul_rn(cz, cz));
@@ -229,31 +270,24 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                 const int khi_t = khi_f < 0.0f ? -1 : (khi_f > (float)(T - 1) ? T - 1 : (int)khi_f);
                 s_lo = klo_t + esub * L;                                                         // this entry's sub-interval
                 s_hi = min(khi_t, s_lo + L - 1);
+                split = khi_t - klo_t + 1 > L;                                                   // the Gaussian has more than one entry
             }
             if (s_lo > s_hi) continue;                                                           // (cannot happen for a listed entry)
             if (MODE != MODE_COUNT) {
                 const int nbase = (s_lo / BS) * BS;
-                if (nbase != base) {
-                    if (!BWD) {
-                        if (base > -0x40000000) flush(base, min(nbase - base, W));
-                    } else {
-                        const int from = max(base + W, nbase);
-                        refill(from, nbase + W - from);
-                    }
-                    base = nbase;
-                    __syncwarp();
-                }
+                if (nbase != base) advance(nbase);
             }
             const float fRlo = (float)s_lo, fRhi = (float)s_hi;
             const float r_in = fmaf(fRlo - 0.5f, dt, t0), r_out = fmaf(fRhi + 0.5f, dt, t0);    // bin k covers [t0+(k-.5)dt, t0+(k+.5)dt]
-            // accumulators of the backward pass for this (Gaussian, scan point)
+            // accumulators of the backward pass for this pair
             float gax = 0.f, gay = 0.f, gaz = 0.f;                                                  // dL/da
             float g00 = 0.f, g01 = 0.f, g02 = 0.f, g10 = 0.f, g11 = 0.f, g12 = 0.f, g20 = 0.f, g21 = 0.f, g22 = 0.f;   // sum dL/db (x) d
             float gwa = 0.f;                                                                        // dL/d(op*alb)
             bool act = valid && (MODE == MODE_COUNT || opalb > 0.f);
+            float D = 0.f;
             if (act) {
                 // radial reject of this scan point against the entry's bins
-                const float D = sqrtf(d2);
+                D = sqrtf(d2);
                 act = (D + v5.x >= r_in) && (D - v5.x <= r_out);
             }
             if (act) {
@@ -264,6 +298,8 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                 // ---- conservative footprint rectangle in lattice index space
                 int i0 = 0, i1 = A - 1, j0 = 0, j1 = A - 1;
                 if (fast) {
+                    const float th0 = s_pi[PI_TH0 * 32 + lane], idth = s_pi[PI_IDTH * 32 + lane];
+                    const float ph0 = s_pi[PI_PH0 * 32 + lane], idph = s_pi[PI_IDPH * 32 + lane];
                     float qx = fmaxf(fmaxf(lox, -hix), 0.f), qy = fmaxf(fmaxf(loy, -hiy), 0.f);
                     float rmin = sqrtf(qx * qx + qy * qy);
                     float bx = fmaxf(fabsf(lox), fabsf(hix)), by = fmaxf(fabsf(loy), fabsf(hiy));
@@ -279,6 +315,187 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                         j1 = clamp_floor((phhi - ph0) * idph + 0.02f, -1, A - 1);
                     }
                 }
+                // ---- the pair's centre bin: up bins kc + s (s < n_up), down bins kc - 1 - s (s < n_dn)
+                const int kc = (int)rintf(fminf(fmaxf((D - t0) * inv_dt, fRlo), fRhi + 1.0f));
+                const int n_up = s_hi - kc + 1, n_dn = kc - s_lo;
+                const float fkc = (float)kc;
+                const float tkc = fmaf(fkc, dt, t0);
+                float* const hpc = Hw + (kc - base) * NLOS_TILE + lane;      // bin kc ; bin kc+s at hpc[32 s], bin kc-1-s at hpc[-32 (s+1)]
+                f32x2 ACC[FWD ? TR_NH : 1];
+                int nflush = 0;
+                if (FWD) {
+#pragma unroll
+                    for (int s = 0; s < TR_NH; ++s) ACC[s] = 0ull;
+                }
+
+                // ---- ray -> Gaussian in r (shared by all modes)
+                auto ray_setup = [&](int i, int j, bool has, RayQ& R, float& bx, float& by, float& bz) {
+                    const float sth = s_tab[(TAB_STH * A + i) * 32 + lane], cth = s_tab[(TAB_CTH * A + i) * 32 + lane];
+                    const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
+                    const float dx = sth * cph, dy = sth * sph, dz = cth;
+                    bx = M00 * dx + M01 * dy + M02 * dz; by = M10 * dx + M11 * dy + M12 * dz; bz = M20 * dx + M21 * dy + M22 * dz;   // b = M d
+                    const float C = bx * bx + by * by + bz * bz;
+                    const float ab = ax * bx + ay * by + az * bz;
+                    const float iC = rcp_nr(C);
+                    const float rsu = -ab * iC;                                             // closest approach r*
+                    const float px = fmaf(rsu, bx, ax), py = fmaf(rsu, by, ay), pz = fmaf(rsu, bz, az);
+                    const float m2min = px * px + py * py + pz * pz;
+                    const float h2 = (P.mcut2 - m2min) * iC;
+                    const float hh = h2 * rsqrt_approx(fmaxf(h2, 1e-30f)) * inv_dt;          // half width of the cut in bins
+                    const float xc = (rsu - t0) * inv_dt;
+                    const float off = (MODE == MODE_ANA) ? 0.5f : 0.0f;                        // bins are [k-.5, k+.5] for the integral
+                    const float klu = fmaxf(ceilf(xc - hh - off), fRlo), khu = fminf(floorf(xc + hh + off), fRhi);
+                    const bool ok = has && (h2 > 0.f) && (klu <= khu);
+                    R.rs = rsu;
+                    R.gam = -0.5f * LOG2E_F * C;
+                    R.al = -0.5f * LOG2E_F * m2min;
+                    R.sth = sth;
+                    R.kl = ok ? klu : 3.0e9f;
+                    R.kh = ok ? khu : -3.0e9f;
+                };
+                // ---- chain rule of one ray from its moments S_n = sum_k w_k e_k tau_k^n  (tau = r_k - r*)
+                auto ray_chain = [&](int i, int j, float rsu, float S0, float S1, float S2) {
+                    const float sth = s_tab[(TAB_STH * A + i) * 32 + lane], cth = s_tab[(TAB_CTH * A + i) * 32 + lane];
+                    const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
+                    const float dx = sth * cph, dy = sth * sph, dz = cth;
+                    const float bx = M00 * dx + M01 * dy + M02 * dz, by = M10 * dx + M11 * dy + M12 * dz, bz = M20 * dx + M21 * dy + M22 * dz;
+                    const float px = fmaf(rsu, bx, ax), py = fmaf(rsu, by, ay), pz = fmaf(rsu, bz, az);
+                    gwa = fmaf(sth, S0, gwa);
+                    // dL/da = -wt (S0 perp + S1 b) ; dL/db = -wt (r* (S0 perp + S1 b) + S1 perp + S2 b)
+                    const float ux = S0 * px + S1 * bx, uy = S0 * py + S1 * by, uz = S0 * pz + S1 * bz;
+                    const float vx = fmaf(rsu, ux, S1 * px + S2 * bx), vy = fmaf(rsu, uy, S1 * py + S2 * by), vz = fmaf(rsu, uz, S1 * pz + S2 * bz);
+                    const float w_ = opalb * sth;
+                    gax = fmaf(-w_, ux, gax); gay = fmaf(-w_, uy, gay); gaz = fmaf(-w_, uz, gaz);
+                    const float bxw = -w_ * vx, byw = -w_ * vy, bzw = -w_ * vz;
+                    g00 = fmaf(bxw, dx, g00); g01 = fmaf(bxw, dy, g01); g02 = fmaf(bxw, dz, g02);
+                    g10 = fmaf(byw, dx, g10); g11 = fmaf(byw, dy, g11); g12 = fmaf(byw, dz, g12);
+                    g20 = fmaf(bzw, dx, g20); g21 = fmaf(bzw, dy, g21); g22 = fmaf(bzw, dz, g22);
+                };
+                // ---- seeds of one stream at the centre bin.  tc = t(kc) + node offset - r*
+                //      E = {e(kc), e(kc-1)} * weight ; G = {e(kc+1)/e(kc), e(kc-2)/e(kc-1)} ; returns q = e-ratio of ratios
+                auto seed = [&](float gam, float al, float tc, float weight, f32x2& E, f32x2& G, f32x2& Q) {
+                    const float gd = gam * dt;
+                    const float e0 = ex2_approx(fmaf(gam * tc, tc, al)) * weight;
+                    const float gu = ex2_approx(gd * fmaf(2.0f, tc, dt));
+                    const float gm = ex2_approx(gd * fmaf(-2.0f, tc, dt));
+                    const float qv = gu * gm;
+                    E = pack2(e0, e0 * gm);
+                    G = pack2(gu, gm * qv);
+                    Q = pack2(qv, qv);
+                };
+                // ---- forward: n steps (rounded up to 4) of two streams into the register accumulators
+                auto run_fwd = [&](f32x2 E0, f32x2 G0, f32x2 Q0, f32x2 E1, f32x2 G1, f32x2 Q1, int nst) {
+#pragma unroll
+                    for (int s = 0; s < (FWD ? TR_NH : 0); ++s) {
+                        if ((s & 3) == 0 && s >= nst) break;
+                        ACC[s] = add2(ACC[s], add2(E0, E1));
+                        E0 = mul2(E0, G0); E1 = mul2(E1, G1);
+                        G0 = mul2(G0, Q0); G1 = mul2(G1, Q1);
+                    }
+                    nflush = max(nflush, (nst + 3) & ~3);
+                };
+                // ---- backward: prefix-sum moments of two streams against the window's weights
+                //      returns the number of executed steps
+                auto run_bwd = [&](f32x2& E0, f32x2 G0, f32x2 Q0, f32x2& E1, f32x2 G1, f32x2 Q1, int nst, f32x2& A0, f32x2& B0, f32x2& C0, f32x2& A1,
+                                   f32x2& B1, f32x2& C1) -> int {
+                    A0 = 0ull; B0 = 0ull; C0 = 0ull; A1 = 0ull; B1 = 0ull; C1 = 0ull;
+                    const float* pu = hpc;
+                    const float* pd = hpc - NLOS_TILE;
+                    if (!split) {
+                        // reads run at most 3 bins past the entry (guard bins / bins beyond the Gaussian's shell); a direction that would
+                        // leave the window + guard is switched off at a 4-step boundary
+                        const int zu = (n_up + TR_GUARD) & ~3, zd = (n_dn + TR_GUARD) & ~3;
+                        const int zmin = min(zu, zd);
+                        int s = 0;
+                        for (; s < nst; s += 4) {
+                            if (s >= zmin) {
+                                float a, b;
+                                unpack2(E0, a, b); E0 = pack2(s >= zu ? 0.f : a, s >= zd ? 0.f : b);
+                                unpack2(E1, a, b); E1 = pack2(s >= zu ? 0.f : a, s >= zd ? 0.f : b);
+                                if (s >= zu) pu = hpc;                      // keep the (ignored) reads inside the window
+                                if (s >= zd) pd = hpc;
+                            }
+#pragma unroll
+                            for (int jx = 0; jx < 4; ++jx) {
+                                const f32x2 w2 = pack2(pu[jx * NLOS_TILE], pd[-jx * NLOS_TILE]);
+                                const f32x2 x0 = mul2(w2, E0), x1 = mul2(w2, E1);
+                                A0 = add2(A0, x0); A1 = add2(A1, x1);
+                                B0 = add2(B0, A0); B1 = add2(B1, A1);
+                                C0 = add2(C0, B0); C1 = add2(C1, B1);
+                                E0 = mul2(E0, G0); E1 = mul2(E1, G1);
+                                G0 = mul2(G0, Q0); G1 = mul2(G1, Q1);
+                            }
+                            pu += 4 * NLOS_TILE; pd -= 4 * NLOS_TILE;
+                        }
+                        return s;
+                    } else {
+                        // split entries: exact clipping to the entry's sub-interval, step by step
+                        const int ns = min(nst, max(n_up, n_dn));
+                        for (int s = 0; s < ns; ++s) {
+                            const float wu = s < n_up ? pu[0] : 0.f, wd = s < n_dn ? pd[0] : 0.f;
+                            const f32x2 w2 = pack2(wu, wd);
+                            const f32x2 x0 = mul2(w2, E0), x1 = mul2(w2, E1);
+                            A0 = add2(A0, x0); A1 = add2(A1, x1);
+                            B0 = add2(B0, A0); B1 = add2(B1, A1);
+                            C0 = add2(C0, B0); C1 = add2(C1, B1);
+                            E0 = mul2(E0, G0); E1 = mul2(E1, G1);
+                            G0 = mul2(G0, Q0); G1 = mul2(G1, Q1);
+                            if (s + 1 < n_up) pu += NLOS_TILE;
+                            if (s + 1 < n_dn) pd -= NLOS_TILE;
+                        }
+                        return ns;
+                    }
+                };
+                // ---- direct evaluation of bins [ka, kb] of one ray (numerical: 1 MUFU per bin; analytic: closed-form erf per bin edge)
+                //      forward: into the window; backward: exact moments
+                auto direct = [&](const RayQ& R, int ka, int kb, float& S0, float& S1, float& S2) {
+                    if (ka > kb) return;
+                    const float wt = opalb * R.sth;
+                    if (MODE == MODE_NUM) {
+                        float t = fmaf((float)ka, dt, t0) - R.rs;
+                        float* hp = Hw + (ka - base) * NLOS_TILE + lane;
+                        for (int k = ka; k <= kb; ++k) {
+                            const float ev = ex2_approx(fmaf(R.gam, t * t, R.al));
+                            if (!BWD) {
+                                *hp = fmaf(wt, ev, *hp);
+                            } else {
+                                const float we = *hp * ev, wet = we * t;
+                                S0 += we; S1 += wet; S2 = fmaf(wet, t, S2);
+                            }
+                            t += dt;
+                            hp += NLOS_TILE;
+                        }
+                    } else if (MODE == MODE_ANA) {
+                        // integral of exp(-C tau^2 / 2) e^{-m2min/2} over bin k = pref [erf(sq tau1) - erf(sq tau0)]  
+                        const float C = R.gam * (-2.0f / LOG2E_F);
+                        const float sq = sqrtf(0.5f * C), iC = 1.0f / C;
+                        const float pk = ex2_approx(R.al);                                       // e^{-m2min/2}
+                        const float pref = SQRT_PI_2 * rsqrt_approx(C) * pk;
+                        float tau = fmaf((float)ka - 0.5f, dt, t0) - R.rs;                       // lower edge of bin ka
+                        float Ep = erf_fast(sq * tau);
+                        float fp = BWD ? pk * ex2_approx(R.gam * tau * tau) : 0.f;
+                        float* hp = Hw + (ka - base) * NLOS_TILE + lane;
+                        for (int k = ka; k <= kb; ++k) {
+                            const float tn = tau + dt;
+                            const float En = erf_fast(sq * tn);
+                            const float Ik = pref * (En - Ep);
+                            if (!BWD) {
+                                *hp = fmaf(wt, Ik, *hp);
+                            } else {
+                                // int tau f = -[f]/C ; int tau^2 f = (int f - [tau f]) / C
+                                const float fn = pk * ex2_approx(R.gam * tn * tn);
+                                const float w = *hp;
+                                S0 = fmaf(w, Ik, S0);
+                                S1 = fmaf(w, -(fn - fp) * iC, S1);
+                                S2 = fmaf(w, (Ik - (tn * fn - tau * fp)) * iC, S2);
+                                fp = fn;
+                            }
+                            Ep = En; tau = tn;
+                            hp += NLOS_TILE;
+                        }
+                    }
+                };
+
                 int wb_lo = 0x7fffffff, wb_hi = -1;
                 for (int ib = i0; ib <= i1; ib += 4)
                     for (int jb = j0; jb <= j1; jb += 8) {
@@ -308,270 +525,125 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                 }
                             }
                         }
-                        // ---- 2. consume the hits RC at a time
+                        // ---- 2. consume the hits
                         while (mask) {
-                            float rs[RC], gam[RC], al[RC], kl[RC], kh[RC], wt[RC];
+                            RayQ R[RC];
                             int bits[RC];
-                            float kminf = 3.0e9f, kmaxf = -3.0e9f;
+                            bool any = false;
                             int bit = 0;
 #pragma unroll
                             for (int u = 0; u < RC; ++u) {
                                 const bool has = mask != 0;
                                 if (has) { bit = __ffs(mask) - 1; mask &= mask - 1; }
                                 bits[u] = bit;
-                                const int i = ib + (bit >> 3), j = jb + (bit & 7);
-                                const float sth = s_tab[(TAB_STH * A + i) * 32 + lane], cth = s_tab[(TAB_CTH * A + i) * 32 + lane];
-                                const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
-                                const float dx = sth * cph, dy = sth * sph, dz = cth;
-                                const float bx = M00 * dx + M01 * dy + M02 * dz, by = M10 * dx + M11 * dy + M12 * dz,
-                                            bz = M20 * dx + M21 * dy + M22 * dz;                            // b = M d
-                                const float C = bx * bx + by * by + bz * bz;
-                                const float ab = ax * bx + ay * by + az * bz;
-                                const float iC = rcp_nr(C);
-                                const float rsu = -ab * iC;                                             // closest approach r*
-                                const float px = fmaf(rsu, bx, ax), py = fmaf(rsu, by, ay), pz = fmaf(rsu, bz, az);
-                                const float m2min = px * px + py * py + pz * pz;
-                                const float h2 = (P.mcut2 - m2min) * iC;
-                                const float hh = h2 * rsqrt_approx(fmaxf(h2, 1e-30f)) * inv_dt;          // half width of the cut in bins
-                                const float xc = (rsu - t0) * inv_dt;
-                                const float off = (MODE == MODE_ANA) ? 0.5f : 0.0f;                        // bins are [k-.5, k+.5] for the integral
-                                const float klu = fmaxf(ceilf(xc - hh - off), fRlo), khu = fminf(floorf(xc + hh + off), fRhi);
-                                const bool ok = has && (h2 > 0.f) && (klu <= khu);
-                                rs[u] = rsu;
-                                gam[u] = -0.5f * LOG2E_F * C;
-                                al[u] = -0.5f * LOG2E_F * m2min;
-                                wt[u] = opalb * sth;
-                                kl[u] = ok ? klu : 3.0e9f;
-                                kh[u] = ok ? khu : -3.0e9f;
-                                kminf = fminf(kminf, kl[u]);
-                                kmaxf = fmaxf(kmaxf, kh[u]);
+                                float bx, by, bz;
+                                ray_setup(ib + (bit >> 3), jb + (bit & 7), has, R[u], bx, by, bz);
+                                any = any || (R[u].kl <= R[u].kh);
                             }
-                            if (kminf > kmaxf) continue;
-                            const int kmin = (int)kminf, kmax = (int)kmaxf;
-                            const float tk0 = fmaf(kminf, dt, t0);
+                            if (!any) continue;
                             if (MODE == MODE_COUNT) {
 #pragma unroll
                                 for (int u = 0; u < RC; ++u)
-                                    if (kl[u] <= kh[u]) c_ev += (unsigned long long)(kmax - kmin + 1);
+                                    if (R[u].kl <= R[u].kh) {
+                                        const int hu = max((int)R[u].kh - kc + 1, kc - (int)R[u].kl);
+                                        c_ev += (unsigned long long)(2 * ((max(hu, 0) + 3) & ~3));
+                                    }
                             } else if (MODE == MODE_NUM) {
-                                // ---- numerical mode: recurrence  e_{k+1} = e_k g_k ; g_{k+1} = g_k q   per ray, common bin loop
-                                float e[RC], g[RC], qq[RC];
-                                float S0[RC], S1[RC], S2[RC];
-                                bool fr[RC];
-                                bool anyfast = false, anyslow = false;
+                                // ---- numerical mode: two rays = two streams
+                                f32x2 E[2], G[2], Q[2];
+                                bool fr[2];
+                                int nst = 0;
+                                const int cap = FWD ? TR_NH : 0x7fffffff;
 #pragma unroll
-                                for (int u = 0; u < RC; ++u) {
-                                    const float tu = tk0 - rs[u];
-                                    const float Lg = fmaf(gam[u] * tu, tu, al[u]);
-                                    const bool vu = kl[u] <= kh[u];
-                                    fr[u] = vu && (Lg > -100.f) && (gam[u] * dt2 > -6.f);     // seed representable, recurrence well-conditioned
-                                    anyfast = anyfast || fr[u];
-                                    anyslow = anyslow || (vu && !fr[u]);
-                                    qq[u] = ex2_approx(2.0f * gam[u] * dt2);
-                                    S0[u] = 0.f; S1[u] = 0.f; S2[u] = 0.f;
+                                for (int u = 0; u < 2; ++u) {
+                                    const bool vu = R[u].kl <= R[u].kh;
+                                    const float tc = tkc - R[u].rs;
+                                    const float Lc = fmaf(R[u].gam * tc, tc, R[u].al);
+                                    fr[u] = vu && (Lc > -100.f) && (R[u].gam * dt2 > -6.f);       // seed representable, recurrence well-conditioned
+                                    seed(R[u].gam, R[u].al, tc, BWD ? 1.0f : opalb * R[u].sth, E[u], G[u], Q[u]);
+                                    if (!fr[u]) { E[u] = 0ull; G[u] = 0ull; }
+                                    const int hu = fr[u] ? max((int)R[u].kh - kc + 1, kc - (int)R[u].kl) : 0;
+                                    nst = max(nst, min(hu, cap));
                                 }
-                                const float kfc = 0.5f * (kmaxf - kminf);                    // moments are taken about the middle of the chunk's bins
-                                if (anyfast) {
-                                    float kf = -kfc;
-                                    const f32x2 q01 = pack2(qq[0], qq[1]), q23 = pack2(qq[2], qq[3]);
-                                    f32x2 A01 = 0ull, A23 = 0ull, B01 = 0ull, B23 = 0ull, C01 = 0ull, C23 = 0ull;     // packed moments
-                                    for (int ks = kmin; ks <= kmax;) {
-                                        const int nseg = min(min(TR_SEG, kmax - ks + 1), W - wrap(ks));      // never across the ring's wrap
-                                        const float tks = fmaf((float)ks, dt, t0);
-                                        float* hp = Hw + wrap(ks) * NLOS_TILE + lane;
-#pragma unroll
-                                        for (int u = 0; u < RC; ++u) {
-                                            const float tu = tks - rs[u];
-                                            const float gt = gam[u] * tu;
-                                            const float ev = ex2_approx(fmaf(gt, tu, al[u]));
-                                            const float gv = ex2_approx(fmaf(2.0f * gt, dt, gam[u] * dt2));
-                                            e[u] = fr[u] ? (BWD ? ev : wt[u] * ev) : 0.f;
-                                            g[u] = fr[u] ? gv : 0.f;
-                                        }
-                                        // packed fp32x2: rays (0,1) and (2,3) share one FMUL2 / FADD2 / FFMA2 each
-                                        f32x2 e01 = pack2(e[0], e[1]), e23 = pack2(e[2], e[3]);
-                                        f32x2 g01 = pack2(g[0], g[1]), g23 = pack2(g[2], g[3]);
-                                        if (!BWD) {
-#pragma unroll 4
-                                            for (int kk = 0; kk < nseg; ++kk) {
-                                                float lo, hi;
-                                                unpack2(add2(e01, e23), lo, hi);
-                                                e01 = mul2(e01, g01); e23 = mul2(e23, g23);
-                                                g01 = mul2(g01, q01); g23 = mul2(g23, q23);
-                                                *hp += lo + hi;
-                                                hp += NLOS_TILE;
-                                            }
-                                        } else {
-#pragma unroll 2
-                                            for (int kk = 0; kk < nseg; ++kk) {
-                                                const float w = *hp;
-                                                const f32x2 w2 = pack2(w, w), k2 = pack2(kf, kf);
-                                                const f32x2 we01 = mul2(w2, e01), we23 = mul2(w2, e23);
-                                                const f32x2 wk01 = mul2(we01, k2), wk23 = mul2(we23, k2);
-                                                A01 = add2(A01, we01); A23 = add2(A23, we23);
-                                                B01 = add2(B01, wk01); B23 = add2(B23, wk23);
-                                                C01 = fma2(wk01, k2, C01); C23 = fma2(wk23, k2, C23);
-                                                e01 = mul2(e01, g01); e23 = mul2(e23, g23);
-                                                g01 = mul2(g01, q01); g23 = mul2(g23, q23);
-                                                kf += 1.0f;
-                                                hp += NLOS_TILE;
-                                            }
-                                        }
-                                        ks += nseg;
-                                    }
-                                    if (BWD) {
-                                        unpack2(A01, S0[0], S0[1]); unpack2(A23, S0[2], S0[3]);
-                                        unpack2(B01, S1[0], S1[1]); unpack2(B23, S1[2], S1[3]);
-                                        unpack2(C01, S2[0], S2[1]); unpack2(C23, S2[2], S2[3]);
+                                float S0[2] = {0.f, 0.f}, S1[2] = {0.f, 0.f}, S2[2] = {0.f, 0.f};
+                                if (nst > 0) {
+                                    if (!BWD) {
+                                        run_fwd(E[0], G[0], Q[0], E[1], G[1], Q[1], nst);
+                                    } else {
+                                        f32x2 A0, B0, C0, A1, B1, C1;
+                                        const int ne = run_bwd(E[0], G[0], Q[0], E[1], G[1], Q[1], nst, A0, B0, C0, A1, B1, C1);
+                                        stream_moments(A0, B0, C0, (float)ne, tkc - R[0].rs, dt, S0[0], S1[0], S2[0]);
+                                        stream_moments(A1, B1, C1, (float)ne, tkc - R[1].rs, dt, S0[1], S1[1], S2[1]);
                                     }
                                 }
-                                if (BWD) {
-                                    // moments about the chunk centre -> moments of tau = r_k - r*
-                                    const float tcen = fmaf(kfc, dt, tk0);
 #pragma unroll
-                                    for (int u = 0; u < RC; ++u) {
-                                        const float tc = tcen - rs[u];
-                                        const float m0 = S0[u], m1 = S1[u] * dt, m2 = S2[u] * dt2;
-                                        S1[u] = fmaf(tc, m0, m1);
-                                        S2[u] = fmaf(tc, fmaf(tc, m0, 2.0f * m1), m2);
+                                for (int u = 0; u < 2; ++u) {
+                                    if (!(R[u].kl <= R[u].kh)) continue;
+                                    const int kl = (int)R[u].kl, kh = (int)R[u].kh;
+                                    if (!fr[u]) {
+                                        direct(R[u], kl, kh, S0[u], S1[u], S2[u]);
+                                    } else if (FWD) {                                      // bins beyond the register accumulators
+                                        direct(R[u], kl, min(kh, kc - TR_NH - 1), S0[u], S1[u], S2[u]);
+                                        direct(R[u], max(kl, kc + TR_NH), kh, S0[u], S1[u], S2[u]);
                                     }
-                                }
-                                if (anyslow) {
-                                    // direct evaluation, 1 MUFU per bin, for rays the recurrence cannot carry
-#pragma unroll
-                                    for (int u = 0; u < RC; ++u) {
-                                        if (!(kl[u] <= kh[u]) || fr[u]) continue;
-                                        const int klo = (int)kl[u], khi = (int)kh[u];
-                                        float t = fmaf((float)klo, dt, t0) - rs[u];
-                                        float a0 = 0.f, a1 = 0.f, a2 = 0.f;
-                                        for (int k = klo; k <= khi; ++k) {
-                                            float* hp = Hw + wrap(k) * NLOS_TILE + lane;
-                                            const float ev = ex2_approx(fmaf(gam[u], t * t, al[u]));
-                                            if (!BWD) {
-                                                *hp = fmaf(wt[u], ev, *hp);
-                                            } else {
-                                                const float we = *hp * ev, wet = we * t;
-                                                a0 += we; a1 += wet; a2 = fmaf(wet, t, a2);
-                                            }
-                                            t += dt;
-                                        }
-                                        if (BWD) { S0[u] = a0; S1[u] = a1; S2[u] = a2; }
-                                    }
-                                }
-                                if (BWD) {
-#pragma unroll
-                                    for (int u = 0; u < RC; ++u) {
-                                        if (!(kl[u] <= kh[u])) continue;
-                                        const int i = ib + (bits[u] >> 3), j = jb + (bits[u] & 7);
-                                        const float sth = s_tab[(TAB_STH * A + i) * 32 + lane], cth = s_tab[(TAB_CTH * A + i) * 32 + lane];
-                                        const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
-                                        const float dx = sth * cph, dy = sth * sph, dz = cth;
-                                        const float bx = M00 * dx + M01 * dy + M02 * dz, by = M10 * dx + M11 * dy + M12 * dz,
-                                                    bz = M20 * dx + M21 * dy + M22 * dz;
-                                        const float px = fmaf(rs[u], bx, ax), py = fmaf(rs[u], by, ay), pz = fmaf(rs[u], bz, az);
-                                        gwa = fmaf(sth, S0[u], gwa);
-                                        // dL/da = -wt (S0 perp + S1 b) ; dL/db = -wt (r* (S0 perp + S1 b) + S1 perp + S2 b)
-                                        const float ux = S0[u] * px + S1[u] * bx, uy = S0[u] * py + S1[u] * by, uz = S0[u] * pz + S1[u] * bz;
-                                        const float vx = fmaf(rs[u], ux, S1[u] * px + S2[u] * bx), vy = fmaf(rs[u], uy, S1[u] * py + S2[u] * by),
-                                                    vz = fmaf(rs[u], uz, S1[u] * pz + S2[u] * bz);
-                                        const float w_ = wt[u];
-                                        gax = fmaf(-w_, ux, gax); gay = fmaf(-w_, uy, gay); gaz = fmaf(-w_, uz, gaz);
-                                        const float bxw = -w_ * vx, byw = -w_ * vy, bzw = -w_ * vz;
-                                        g00 = fmaf(bxw, dx, g00); g01 = fmaf(bxw, dy, g01); g02 = fmaf(bxw, dz, g02);
-                                        g10 = fmaf(byw, dx, g10); g11 = fmaf(byw, dy, g11); g12 = fmaf(byw, dz, g12);
-                                        g20 = fmaf(bzw, dx, g20); g21 = fmaf(bzw, dy, g21); g22 = fmaf(bzw, dz, g22);
-                                    }
+                                    if (BWD) ray_chain(ib + (bits[u] >> 3), jb + (bits[u] & 7), R[u].rs, S0[u], S1[u], S2[u]);
                                 }
                             } else {
-                                // ---- MODE_ANA : exact bin integrals, erf shared between adjacent bin edges
-                                float sq[RC], pref[RC], u0[RC], Ep[RC];
-                                float Dp[RC], DUp[RC], F[RC], P1[RC], P2[RC];
-                                const float ue = fmaf(-0.5f, dt, tk0);                           // lower edge of bin kmin
-#pragma unroll
-                                for (int u = 0; u < RC; ++u) {
-                                    const bool vu = kl[u] <= kh[u];
-                                    const float C = gam[u] * (-2.0f / LOG2E_F);
-                                    sq[u] = vu ? sqrtf(0.5f * C) : 0.f;
-                                    pref[u] = vu ? 1.2533141373155001f * rsqrt_approx(C) * ex2_approx(al[u]) : 0.f;     // sqrt(pi/(2C)) e^{-m2min/2}
-                                    u0[u] = ue - rs[u];
-                                    const float z = sq[u] * u0[u];
-                                    Ep[u] = erf_fast(z);
-                                    if (BWD) {
-                                        Dp[u] = TWO_OVER_SQRT_PI * ex2_approx(-LOG2E_F * z * z);
-                                        DUp[u] = Dp[u] * u0[u];
-                                        F[u] = 0.f; P1[u] = 0.f; P2[u] = 0.f;
-                                    }
-                                }
-                                {
-                                    float kf = 1.0f;
-                                    if (!BWD) {
-#pragma unroll 2
-                                        for (int k = kmin; k <= kmax; ++k) {
-                                            float acc = 0.f;
-#pragma unroll
-                                            for (int u = 0; u < RC; ++u) {
-                                                const float E = erf_fast(sq[u] * fmaf(kf, dt, u0[u]));
-                                                acc = fmaf(wt[u] * pref[u], E - Ep[u], acc);
-                                                Ep[u] = E;
-                                            }
-                                            Hw[wrap(k) * NLOS_TILE + lane] += acc;
-                                            kf += 1.0f;
-                                        }
-                                    } else {
-                                        for (int k = kmin; k <= kmax; ++k) {
-                                            const float w = Hw[wrap(k) * NLOS_TILE + lane];
-#pragma unroll
-                                            for (int u = 0; u < RC; ++u) {
-                                                const float uu = fmaf(kf, dt, u0[u]);
-                                                const float z = sq[u] * uu;
-                                                const float E = erf_fast(z);
-                                                const float Dn = TWO_OVER_SQRT_PI * ex2_approx(-LOG2E_F * z * z);
-                                                const float DUn = Dn * uu;
-                                                F[u] = fmaf(w, E - Ep[u], F[u]);
-                                                P1[u] = fmaf(w, Dn - Dp[u], P1[u]);
-                                                P2[u] = fmaf(w, DUn - DUp[u], P2[u]);
-                                                Ep[u] = E; Dp[u] = Dn; DUp[u] = DUn;
-                                            }
-                                            kf += 1.0f;
+                                // ---- analytic-exact mode: one ray, Gauss-Legendre nodes +-x (pairs) per bin
+                                const RayQ& r = R[0];
+                                const int kl = (int)r.kl, kh = (int)r.kh;
+                                const float gp = -r.gam * dt2;                               // 0.72 / (sigma in bins)^2
+                                const float tc = tkc - r.rs;
+                                const float tfar = fabsf(tc) + 0.5f * dt;
+                                const bool fr = (gp <= 2.0f) && (fmaf(r.gam * tfar, tfar, r.al) > -100.f);
+                                float S0 = 0.f, S1 = 0.f, S2 = 0.f;
+                                if (!fr) {
+                                    direct(r, kl, kh, S0, S1, S2);
+                                } else {
+                                    const int npass = gp <= 0.08f ? 1 : 2;                   // GL2 (sigma >= 3 bins) or GL4
+                                    const int cap = FWD ? TR_NH : 0x7fffffff;
+                                    const int nst = min(max(kh - kc + 1, kc - kl), cap);
+                                    const float wbase = (BWD ? 1.0f : opalb * r.sth) * dt;
+                                    for (int ps = 0; ps < npass; ++ps) {
+                                        const float xn = (npass == 1 ? 0.28867513459481287f : (ps == 0 ? 0.16999052179242816f : 0.43056815579702626f)) * dt;
+                                        const float wn = (npass == 1 ? 0.5f : (ps == 0 ? 0.32607257743127305f : 0.17392742256872692f)) * wbase;
+                                        f32x2 E0, G0, Q0, E1, G1, Q1;
+                                        seed(r.gam, r.al, tc + xn, wn, E0, G0, Q0);
+                                        seed(r.gam, r.al, tc - xn, wn, E1, G1, Q1);
+                                        if (!BWD) {
+                                            run_fwd(E0, G0, Q0, E1, G1, Q1, nst);
+                                        } else {
+                                            f32x2 A0, B0, C0, A1, B1, C1;
+                                            const int ne = run_bwd(E0, G0, Q0, E1, G1, Q1, nst, A0, B0, C0, A1, B1, C1);
+                                            stream_moments(A0, B0, C0, (float)ne, tc + xn, dt, S0, S1, S2);
+                                            stream_moments(A1, B1, C1, (float)ne, tc - xn, dt, S0, S1, S2);
                                         }
                                     }
-                                }
-                                if (BWD) {
-#pragma unroll
-                                    for (int u = 0; u < RC; ++u) {
-                                        if (!(kl[u] <= kh[u])) continue;
-                                        const int i = ib + (bits[u] >> 3), j = jb + (bits[u] & 7);
-                                        const float sth = s_tab[(TAB_STH * A + i) * 32 + lane], cth = s_tab[(TAB_CTH * A + i) * 32 + lane];
-                                        const float sph = s_tab[(TAB_SPH * A + j) * 32 + lane], cph = s_tab[(TAB_CPH * A + j) * 32 + lane];
-                                        const float dx = sth * cph, dy = sth * sph, dz = cth;
-                                        const float bx = M00 * dx + M01 * dy + M02 * dz, by = M10 * dx + M11 * dy + M12 * dz,
-                                                    bz = M20 * dx + M21 * dy + M22 * dz;
-                                        const float rsu = rs[u], w_ = wt[u];
-                                        const float px = fmaf(rsu, bx, ax), py = fmaf(rsu, by, ay), pz = fmaf(rsu, bz, az);
-                                        const float C = gam[u] * (-2.0f / LOG2E_F);
-                                        gwa = fmaf(sth * pref[u], F[u], gwa);
-                                        const float iC = 1.0f / C;
-                                        const float gpref = w_ * F[u], gsq = w_ * pref[u] * P2[u], grs = -w_ * pref[u] * sq[u] * P1[u];
-                                        const float gm = -0.5f * gpref * pref[u];
-                                        const float k1 = grs * iC;                                  // multiplies (perp + r* b) and b
-                                        const float k2 = gsq / (2.0f * sq[u]) - gpref * pref[u] * iC;     // multiplies b
-                                        // dL/da = 2 gm perp - k1 b ;  dL/db = 2 gm r* perp - k1 (perp + r* b) + k2 b
-                                        const float dax = 2.f * gm * px - k1 * bx, day = 2.f * gm * py - k1 * by, daz = 2.f * gm * pz - k1 * bz;
-                                        const float dbx = 2.f * gm * rsu * px - k1 * fmaf(rsu, bx, px) + k2 * bx;
-                                        const float dby = 2.f * gm * rsu * py - k1 * fmaf(rsu, by, py) + k2 * by;
-                                        const float dbz = 2.f * gm * rsu * pz - k1 * fmaf(rsu, bz, pz) + k2 * bz;
-                                        gax += dax; gay += day; gaz += daz;
-                                        g00 = fmaf(dbx, dx, g00); g01 = fmaf(dbx, dy, g01); g02 = fmaf(dbx, dz, g02);
-                                        g10 = fmaf(dby, dx, g10); g11 = fmaf(dby, dy, g11); g12 = fmaf(dby, dz, g12);
-                                        g20 = fmaf(dbz, dx, g20); g21 = fmaf(dbz, dy, g21); g22 = fmaf(dbz, dz, g22);
+                                    if (FWD) {
+                                        direct(r, kl, min(kh, kc - TR_NH - 1), S0, S1, S2);
+                                        direct(r, max(kl, kc + TR_NH), kh, S0, S1, S2);
                                     }
                                 }
+                                if (BWD) ray_chain(ib + (bits[0] >> 3), jb + (bits[0] & 7), r.rs, S0, S1, S2);
                             }
                         }
                     }
                 if (MODE == MODE_COUNT && wb_hi >= wb_lo) c_wb += wb_hi - wb_lo + 1;
+                // ---- forward: merge the pair's register accumulators into the window (clipped to the entry's sub-interval)
+                if (FWD && nflush > 0) {
+                    const int nu = min(nflush, n_up), nd = min(nflush, n_dn);
+                    const int nm = max(nu, nd);
+#pragma unroll
+                    for (int s = 0; s < (FWD ? TR_NH : 0); ++s) {
+                        if ((s & 3) == 0 && s >= nm) break;
+                        float lo, hi;
+                        unpack2(ACC[s], lo, hi);
+                        if (s < nu) hpc[s * NLOS_TILE] += lo;
+                        if (s < nd) hpc[-(s + 1) * NLOS_TILE] += hi;
+                    }
+                }
             }
-            if (BWD && MODE != MODE_COUNT) {
+            if (GRAD) {
                 // a = M (o - mu) = -M c :  dL/dM += dL/da (x) (o - mu) ;  dL/dmu = -M^T dL/da
                 float o[13];
                 o[0] = fmaf(-gax, cx, g00); o[1] = fmaf(-gax, cy, g01); o[2] = fmaf(-gax, cz, g02);
@@ -613,15 +685,15 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
         }
         return;
     }
-    if (!BWD && base > -0x40000000) {
+    if (!BWD && base != NO_BASE) {
         __syncwarp();
-        flush(base, W);
+        flush(W);
     }
 }
 
 static size_t transient_smem_bytes(int A, int window)
 {
-    size_t f = (size_t)(NLOS_NTAB * A + NLOS_PINFO_ROWS) * NLOS_TILE + (size_t)TR_WPB * window * NLOS_TILE +
+    size_t f = (size_t)(NLOS_NTAB * A + NLOS_PINFO_ROWS) * NLOS_TILE + (size_t)TR_WPB * (window + 2 * TR_GUARD) * NLOS_TILE +
                (size_t)TR_WPB * TR_STAGES * TR_RING * NLOS_REC_FLOATS;
     return f * 4 + (1 + TR_WPB * TR_STAGES) * 8 + 16;
 }
