@@ -66,17 +66,18 @@ int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float
 
 /* ---- batched transient H[n_tiles*32, T] and its backward.  mode 0 = numerical (volume_renderer.cu
  * no-occlusion branch :139-182), 1 = analytic-exact per-bin integral.
- * bin k sits at radius t0 + k*dt.  H and dacc are zeroed by the callee. */
+ * bin k sits at radius t0 + k*dt.  H and dacc are zeroed by the callee.  `work` is int32 scratch [n_tiles] (zeroed by the callee):
+ * the per-tile slice counters the persistent CTAs pull work from; slice_len = list entries a warp takes at a time. */
 int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                               const long long* cell_offsets, const int* tile_items, int n_cta_items, float t0, float dt, int T,
+                               const long long* cell_offsets, int* work, float t0, float dt, int T,
                                int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, float* H, void* stream);
 int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                const long long* cell_offsets, const int* tile_items, int n_cta_items, float t0, float dt, int T,
+                                const long long* cell_offsets, int* work, float t0, float dt, int T,
                                 int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, const float* grad_H,
                                 float* dacc, void* stream);
 /* counters uint64 [4]: hit (g,ray) pairs, W_s, sample-evals evaluated, W_b */
 int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                             const long long* cell_offsets, const int* tile_items, int n_cta_items, float t0, float dt, int T,
+                             const long long* cell_offsets, int* work, float t0, float dt, int T,
                              int window, int bucket, int slice_len, float mcut, unsigned long long* counters, void* stream);
 
 /* ==== one-scan-point operators: the reference's pybind module nlos_gaussian_renderer._C ===========================

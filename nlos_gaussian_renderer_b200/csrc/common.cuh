@@ -28,14 +28,19 @@
 #define REC_RAD 20    // mcut * max(scale)
 #define REC_S 21      // 21..23 activated scales
 
-// lattice tables per tile: [NLOS_NTAB][A][32]
-#define TAB_STH 0
-#define TAB_CTH 1
-#define TAB_TTH 2     // sin/cos (theta)
-#define TAB_SPH 3
-#define TAB_CPH 4
-#define TAB_ISPH 5    // 1/sin(phi)
-#define TAB_ICPH 6    // 1/cos(phi)
+// lattice tables per tile (NLOS_NTAB * A rows of 32 lanes):
+//   theta block  [A][3][32] : row i -> sin(theta_i), cos(theta_i), tan(theta_i)
+//   phi block    [A][4][32] : row j -> sin(phi_j), cos(phi_j), 1/sin(phi_j), 1/cos(phi_j)
+// so that ONE address per lattice index reaches all of its values with immediate offsets.
+#define TAB_TH(A, i) ((i) * 96)                      // float offset of theta row i
+#define TAB_PH(A, j) (3 * (A) * 32 + (j) * 128)      // float offset of phi row j
+#define TH_SIN 0
+#define TH_COS 32
+#define TH_TAN 64
+#define PH_SIN 0
+#define PH_COS 32
+#define PH_ISIN 64
+#define PH_ICOS 96
 // pinfo rows: [NLOS_PINFO_ROWS][32]
 #define PI_OX 0
 #define PI_OY 1
@@ -196,6 +201,20 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
     f32x2 r;
     asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
     return r;
+}
+
+// in-place forms (the accumulator is both source and destination: keeps unrolled register arrays in place)
+__device__ __forceinline__ void acc_add2(f32x2& a, f32x2 b)
+{
+    asm("add.rn.f32x2 %0, %0, %1;" : "+l"(a) : "l"(b));
+}
+__device__ __forceinline__ void acc_mul2(f32x2& a, f32x2 b)
+{
+    asm("mul.rn.f32x2 %0, %0, %1;" : "+l"(a) : "l"(b));
+}
+__device__ __forceinline__ void acc_fma2(f32x2& c, f32x2 a, f32x2 b)
+{
+    asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(c) : "l"(a), "l"(b));
 }
 
 __device__ __forceinline__ float warp_sum(float v)

@@ -189,7 +189,7 @@ extern "C" int nlosb200_compute_bboxes(const float* means, const float* log_scal
 
 // ------------------------------------------------------------------------------------------------
 // Scan-tile tables.  A tile = 32 consecutive scan points (caller orders them tile-major); per tile one
-// contiguous block [NLOS_NTAB][A][32] + [NLOS_PINFO_ROWS][32] floats that the render kernels pull into
+// contiguous block theta [A][3][32] + phi [A][4][32] (common.cuh) + [NLOS_PINFO_ROWS][32] floats that the render kernels pull into
 // shared memory with ONE TMA bulk copy.  The lattice follows gaussian_model/cuda_autograd.py:254-268:
 // theta_i / phi_j = linspace(min, max, A); the caller passes the sin/cos tables it built with torch so
 // that this path and the oracle consume identical ray directions.
@@ -210,13 +210,13 @@ __global__ void __launch_bounds__(128) build_scan_tiles_kernel(const float* __re
     for (int i = 0; i < A; ++i) {
         float st = valid ? sin_th[(size_t)p * A + i] : 1.f, ct = valid ? cos_th[(size_t)p * A + i] : 1.f;
         float sp = valid ? sin_ph[(size_t)p * A + i] : 1.f, cp = valid ? cos_ph[(size_t)p * A + i] : 1.f;
-        tb[(TAB_STH * A + i) * NLOS_TILE + lane] = st;
-        tb[(TAB_CTH * A + i) * NLOS_TILE + lane] = ct;
-        tb[(TAB_TTH * A + i) * NLOS_TILE + lane] = __fdiv_rn(st, ct);
-        tb[(TAB_SPH * A + i) * NLOS_TILE + lane] = sp;
-        tb[(TAB_CPH * A + i) * NLOS_TILE + lane] = cp;
-        tb[(TAB_ISPH * A + i) * NLOS_TILE + lane] = __frcp_rn(sp);
-        tb[(TAB_ICPH * A + i) * NLOS_TILE + lane] = __frcp_rn(cp);
+        tb[TAB_TH(A, i) + TH_SIN + lane] = st;
+        tb[TAB_TH(A, i) + TH_COS + lane] = ct;
+        tb[TAB_TH(A, i) + TH_TAN + lane] = __fdiv_rn(st, ct);
+        tb[TAB_PH(A, i) + PH_SIN + lane] = sp;
+        tb[TAB_PH(A, i) + PH_COS + lane] = cp;
+        tb[TAB_PH(A, i) + PH_ISIN + lane] = __frcp_rn(sp);
+        tb[TAB_PH(A, i) + PH_ICOS + lane] = __frcp_rn(cp);
     }
     float th0 = 0.f, dth = 0.f, ph0 = 0.f, dph = 0.f;
     if (valid) { th0 = lattice[4 * p + 0]; dth = lattice[4 * p + 1]; ph0 = lattice[4 * p + 2]; dph = lattice[4 * p + 3]; }

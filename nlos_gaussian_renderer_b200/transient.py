@@ -28,8 +28,8 @@ class TransientRenderer:
     def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
                  mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0):
         """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
-        (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries per warp (default: sized so that
-        the grid is a few waves of the 148 SMs)."""
+        (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries a warp pulls at a time from its
+        tile's counter (default: 16..256, sized so that every warp of the persistent grid gets >= 32 slices)."""
         self.geom = geom
         self.T, self.t0, self.dt, self.c_deltaT = int(T), float(t0), float(dt), float(c_deltaT)
         self.mode = MODES[mode] if isinstance(mode, str) else int(mode)
@@ -62,12 +62,13 @@ class TransientRenderer:
         self.cell_counts = torch.empty(n_cells, dtype=torch.int32, device=dev)
         self.cell_offsets = torch.empty(n_cells + 1, dtype=torch.int64, device=dev)
         self.tile_items = torch.empty(self.geom.n_tiles + 1, dtype=torch.int32, device=dev)
+        self.work = torch.empty(self.geom.n_tiles, dtype=torch.int32, device=dev)      # per-tile slice counters (work stealing)
         self.header = torch.zeros(4, dtype=torch.int64, device=dev)
         self.dacc = torch.empty(N, L.nlosb200_grad_floats(), dtype=torch.float32, device=dev)
         self._N = N
         if self.slice_len is None:
             est = self.geom.n_tiles * N * 1.05                    # ~one entry per (tile, Gaussian)
-            self._slice = int(min(1024, max(16, est / (N_SM * self.wpb * 8)))) // 4 * 4      # ~8 waves of one CTA per SM
+            self._slice = int(min(256, max(16, est / (N_SM * self.wpb * 32)))) // 4 * 4      # >= 32 slices per warp: fine-grained stealing
         else:
             self._slice = int(self.slice_len)
 
@@ -101,8 +102,7 @@ class TransientRenderer:
     def _render_args(self):
         g = self.geom
         return (g.tiles().data_ptr(), g.n_tiles, g.A, self.records.data_ptr(), self._N, self._list.data_ptr(),
-                self.cell_offsets.data_ptr(), self.tile_items.data_ptr(), self.n_items, self.t0, self.dt, self.T, self.window, self.bucket,
-                self._slice)
+                self.cell_offsets.data_ptr(), self.work.data_ptr(), self.t0, self.dt, self.T, self.window, self.bucket, self._slice)
 
     def forward_tiled(self):
         """-> H [n_tiles*32, T] in tile-major scan order (after prepare())."""

@@ -30,4 +30,4 @@ for _ in range(reps):
     g = r.backward_tiled(torch.ones_like(H))
     ev[2].record()
     torch.cuda.synchronize()
-    print(f"{cfg} {mode} {kw}: fwd {ev[0].elapsed_time(ev[1]):.2f} ms  bwd {ev[1].elapsed_time(ev[2]):.2f} ms  items {r.n_items} slice {r._slice} list {r.last_total}")
+    print(f"{cfg} {mode} {kw}: fwd {ev[0].elapsed_time(ev[1]):.2f} ms  bwd {ev[1].elapsed_time(ev[2]):.2f} ms  slice {r._slice} list {r.last_total}")
