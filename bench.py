@@ -270,8 +270,19 @@ def run_b200(args):
         peak_fp32 = 148 * 128 * 2 * f_mhz * 1e6 / 1e12                    # TFLOP/s at the SM clock seen during the run
         peak_sfu = 148 * 16 * f_mhz * 1e6                                  # MUFU ops/s
         ws_rank = work["W_s"]                                               # rank 0's kernel
-        fl = FLOPS_PER_EVAL[(args.mode, "bwd")]
-        ach = ws_rank * fl / (bwd_ms * 1e-3) / 1e12
+
+        def roof(kind, ms):
+            """achieved = W_s / t against min(FP32 ceiling, SFU ceiling) for the algorithmic op mix of one sample-eval,
+            expressed in TFLOP/s: peak = min(FP32 peak, SFU rate x flop-per-MUFU of the mix)."""
+            fl, mu = FLOPS_PER_EVAL[(args.mode, kind)], MUFU_PER_EVAL[(args.mode, kind)]
+            ach = ws_rank * fl / (ms * 1e-3) / 1e12
+            sfu_equiv = peak_sfu * fl / mu / 1e12
+            peak = min(peak_fp32, sfu_equiv)
+            return {"launch_ms": ms, "achieved": ach, "peak": peak, "frac": ach / peak, "binding_pipe": "fp32" if peak_fp32 <= sfu_equiv else "sfu",
+                    "fp32_frac": ach / peak_fp32, "sfu_frac": ws_rank * mu / (ms * 1e-3) / peak_sfu, "flop_per_sample_eval": fl,
+                    "mufu_per_sample_eval": mu, "sample_evals_per_s": ws_rank / (ms * 1e-3)}
+
+        rb, rf = roof("bwd", bwd_ms), roof("fwd", fwd_ms)
         n_bytes = N * 12 * 4
         line = {
             "metric": "Gaussian-bin evals/s (forward+backward transient)", "value": Wb / (ms_step * 1e-3), "unit": "Gaussian-bin evals/s",
@@ -287,14 +298,12 @@ def run_b200(args):
             "e2e": {"value": Wb / (ms_e2e / args.steps * 1e-3), "unit": "Gaussian-bin evals/s", "h2d_bytes_per_step": n_bytes,
                     "d2h_bytes_per_step": n_bytes + 4, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": 8 * args.steps,
-            "roofline": {"bound": "fp32", "kernel": f"transient_kernel<{args.mode},bwd>", "achieved": ach, "peak": peak_fp32,
-                         "unit": "TFLOP/s", "frac": ach / peak_fp32, "traffic": None,
-                         "peak_source": f"148 SM x 128 FP32 lanes x 2 flop x {f_mhz} MHz (SM clock sampled during the run); "
-                                        "MEASURED_PEAKS.json holds only HBM and bf16 tensor peaks, neither binds this kernel",
-                         "flop_per_sample_eval": fl, "sample_evals_per_launch": ws_rank, "launch_ms": bwd_ms,
-                         "sfu_frac": ws_rank * MUFU_PER_EVAL[(args.mode, "bwd")] / (bwd_ms * 1e-3) / peak_sfu,
-                         "fwd": {"launch_ms": fwd_ms, "frac": ws_rank * FLOPS_PER_EVAL[(args.mode, "fwd")] / (fwd_ms * 1e-3) / 1e12 / peak_fp32,
-                                 "sfu_frac": ws_rank * MUFU_PER_EVAL[(args.mode, "fwd")] / (fwd_ms * 1e-3) / peak_sfu}},
+            "roofline": {"bound": "compute (" + rb["binding_pipe"] + " pipe)", "kernel": f"transient_kernel<{args.mode},bwd>", "achieved": rb["achieved"],
+                         "peak": rb["peak"], "unit": "TFLOP/s", "frac": rb["frac"], "traffic": None,
+                         "peak_source": f"min(148 SM x 128 FP32 lanes x 2 flop, 148 SM x 16 MUFU/clk x flop-per-MUFU of the algorithmic mix) x {f_mhz} MHz "
+                                        "(SM clock sampled during the run; SURVEY.md 8d); MEASURED_PEAKS.json holds only HBM and bf16 tensor peaks, "
+                                        "neither binds this kernel (DRAM traffic ~45 MB per launch)",
+                         "sample_evals_per_launch": ws_rank, "bwd": rb, "fwd": rf},
             "loss": float(loss),
         }
         if world == 1 and not args.no_cpu_baseline:

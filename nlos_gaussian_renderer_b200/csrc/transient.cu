@@ -37,7 +37,9 @@
 
 using namespace nlos;
 
+#ifndef TR_WPB
 #define TR_WPB 12          // warps per CTA
+#endif
 #define TR_MINB 1          // CTAs per SM the register allocation is sized for
 #define TR_RING 4          // records per ring stage
 #define TR_STAGES 2
@@ -400,6 +402,38 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                             R.sth = sth;
                             R.tc = dD - R.rsp;
                         };
+                        // the same for two rays at once, one ray in each half of the packed fp32x2 operations (FFMA2/FMUL2)
+                        auto ray_setup2 = [&](const float* tha, const float* pha, const float* thb_, const float* phb_, Ray& Ra, Ray& Rb) {
+                            const f32x2 sth = pack2(tha[TH_SIN], thb_[TH_SIN]), cth = pack2(tha[TH_COS], thb_[TH_COS]);
+                            const f32x2 sph = pack2(pha[PH_SIN], phb_[PH_SIN]), cph = pack2(pha[PH_COS], phb_[PH_COS]);
+                            const f32x2 dx = mul2(sth, cph), dy = mul2(sth, sph);
+                            const f32x2 bx = fma2(pack2(M00, M00), dx, fma2(pack2(M01, M01), dy, mul2(pack2(M02, M02), cth)));
+                            const f32x2 by = fma2(pack2(M10, M10), dx, fma2(pack2(M11, M11), dy, mul2(pack2(M12, M12), cth)));
+                            const f32x2 bz = fma2(pack2(M20, M20), dx, fma2(pack2(M21, M21), dy, mul2(pack2(M22, M22), cth)));
+                            const f32x2 Dv = pack2(D, D);
+                            const f32x2 px = fma2(Dv, bx, pack2(ax, ax)), py = fma2(Dv, by, pack2(ay, ay)), pz = fma2(Dv, bz, pack2(az, az));
+                            const f32x2 C = fma2(bx, bx, fma2(by, by, mul2(bz, bz)));
+                            const f32x2 sp = fma2(px, bx, fma2(py, by, mul2(pz, bz)));
+                            const f32x2 n2 = fma2(px, px, fma2(py, py, mul2(pz, pz)));
+                            float Ca, Cb;
+                            unpack2(C, Ca, Cb);
+                            const f32x2 iC = pack2(rcp_approx(Ca), rcp_approx(Cb));
+                            const f32x2 neg1 = pack2(-1.0f, -1.0f);
+                            const f32x2 rsp = mul2(mul2(sp, neg1), iC);
+                            const f32x2 m2 = fma2(rsp, sp, n2);
+                            const f32x2 h2 = mul2(fma2(m2, neg1, pack2(P.mcut2, P.mcut2)), iC);
+                            const f32x2 gam = mul2(C, pack2(KG, KG)), al = mul2(m2, pack2(KG, KG));
+                            const f32x2 tc = fma2(rsp, neg1, pack2(dD, dD));
+                            float h2a, h2b;
+                            unpack2(h2, h2a, h2b);
+                            Ra.ok = h2a > 0.f; Rb.ok = h2b > 0.f;
+                            Ra.hh = sqrt_approx(h2a) * inv_dt; Rb.hh = sqrt_approx(h2b) * inv_dt;
+                            unpack2(rsp, Ra.rsp, Rb.rsp);
+                            unpack2(gam, Ra.gam, Rb.gam);
+                            unpack2(al, Ra.al, Rb.al);
+                            unpack2(tc, Ra.tc, Rb.tc);
+                            unpack2(sth, Ra.sth, Rb.sth);
+                        };
                         // ---- chain rule of one ray from its moments S_n = sum_k w_k e_k tau_k^n  (tau = r_k - r*)
                         auto ray_chain = [&](const float* th, const float* ph, float rsp, float S0, float S1, float S2) {
                             const float sth = th[TH_SIN], cth = th[TH_COS], sph = ph[PH_SIN], cph = ph[PH_COS];
@@ -481,29 +515,43 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                             for (int jb = j0; jb <= j1; jb += 8) {
                                 const float* const thb = tabl + TAB_TH(A, ib);
                                 const float* const phb = tabl + TAB_PH(A, jb);
-                                // ---- 1. exact slab test of every candidate ray of this 4x8 block -> hit mask (bit = 8*row + column)
+                                // ---- 1. exact slab test of every candidate ray of this 4x8 block -> hit mask (bit = 8*row + column).
+                                //         cuda_utils.cuh:97-121 with every t multiplied by sin(theta) > 0: the x and y slabs then depend on
+                                //         the column only and the z slab on the row only (same operations, same order: bit-exact decisions)
                                 unsigned mask = 0;
                                 const int ni = min(4, i1 - ib + 1), nj = min(8, j1 - jb + 1);
-                                for (int ii = 0; ii < ni; ++ii) {
-                                    const float tth = thb[ii * 96 + TH_TAN];
-                                    const float tz0 = loz * tth, tz1 = hiz * tth;
-                                    const float zmn = fminf(tz0, tz1), zmx = fmaxf(tz0, tz1);
-                                    for (int jj = 0; jj < nj; ++jj) {
-                                        // cuda_utils.cuh:97-121 with every t multiplied by sin(theta) > 0
+                                float xymn[8], xymx[8];
+#pragma unroll
+                                for (int jj = 0; jj < 8; ++jj) {
+                                    xymn[jj] = INFINITY; xymx[jj] = -INFINITY;
+                                    if (jj < nj) {
                                         const float icp = phb[jj * 128 + PH_ICOS], isp = phb[jj * 128 + PH_ISIN];
                                         const float tx0 = lox * icp, tx1 = hix * icp, ty0 = loy * isp, ty1 = hiy * isp;
-                                        const float tmin = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), zmn);
-                                        const float tmax = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), zmx);
-                                        const bool hit = (tmax >= tmin) && (tmax >= 0.f);
-                                        mask |= (hit ? 1u : 0u) << (ii * 8 + jj);
-                                        if (MODE == MODE_COUNT && hit) {
-                                            // slab interval stretched about its midpoint by 5.3/3 (t = t'/sin(theta))
-                                            const float ist = 1.0f / thb[ii * 96 + TH_SIN];
-                                            const float mid = 0.5f * (tmin + tmax) * ist, half = 0.5f * (tmax - tmin) * ist * (5.3f / 3.0f);
-                                            const int ka = clamp_ceil((mid - half - t0) * inv_dt, s_lo, s_hi + 1),
-                                                      kb = clamp_floor((mid + half - t0) * inv_dt, s_lo - 1, s_hi);
-                                            c_hits += (r_in <= mid && mid < r_out) ? 1 : 0;
-                                            if (kb >= ka) { c_ws += kb - ka + 1; wb_lo = min(wb_lo, ka); wb_hi = max(wb_hi, kb); }
+                                        xymn[jj] = fmaxf(fminf(tx0, tx1), fminf(ty0, ty1));
+                                        xymx[jj] = fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1));
+                                    }
+                                }
+#pragma unroll
+                                for (int ii = 0; ii < 4; ++ii) {
+                                    if (ii < ni) {
+                                        const float tth = thb[ii * 96 + TH_TAN];
+                                        const float tz0 = loz * tth, tz1 = hiz * tth;
+                                        const float zmn = fminf(tz0, tz1), zmx = fmaxf(tz0, tz1);
+#pragma unroll
+                                        for (int jj = 0; jj < 8; ++jj) {
+                                            const float tmin = fmaxf(xymn[jj], zmn);
+                                            const float tmax = fminf(xymx[jj], zmx);
+                                            const bool hit = (tmax >= tmin) && (tmax >= 0.f);
+                                            mask |= (hit ? 1u : 0u) << (ii * 8 + jj);
+                                            if (MODE == MODE_COUNT && hit) {
+                                                // slab interval stretched about its midpoint by 5.3/3 (t = t'/sin(theta))
+                                                const float ist = 1.0f / thb[ii * 96 + TH_SIN];
+                                                const float mid = 0.5f * (tmin + tmax) * ist, half = 0.5f * (tmax - tmin) * ist * (5.3f / 3.0f);
+                                                const int ka = clamp_ceil((mid - half - t0) * inv_dt, s_lo, s_hi + 1),
+                                                          kb = clamp_floor((mid + half - t0) * inv_dt, s_lo - 1, s_hi);
+                                                c_hits += (r_in <= mid && mid < r_out) ? 1 : 0;
+                                                if (kb >= ka) { c_ws += kb - ka + 1; wb_lo = min(wb_lo, ka); wb_hi = max(wb_hi, kb); }
+                                            }
                                         }
                                     }
                                 }
@@ -551,8 +599,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         const float* const th1p = thb + (b1 >> 3) * 96;
                                         const float* const ph1p = phb + (b1 & 7) * 128;
                                         Ray R0, R1;
-                                        ray_setup(th0p, ph0p, R0);
-                                        ray_setup(th1p, ph1p, R1);
+                                        ray_setup2(th0p, ph0p, th1p, ph1p, R0, R1);
                                         const bool ok0 = R0.ok, ok1 = has1 && R1.ok;
                                         if (!(ok0 || ok1)) continue;
                                         if (!ok0) { R0.gam = R1.gam; R0.al = R1.al; R0.tc = R1.tc; R0.hh = R1.hh; }
@@ -659,15 +706,26 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                         if (MODE == MODE_COUNT && wb_hi >= wb_lo) c_wb += wb_hi - wb_lo + 1;
                         // ---- forward: merge the pair's register accumulators into the window (clipped to the entry's sub-interval)
                         if (FWD && nflush > 0) {
-                            const int nu = min(nflush, n_up), nd = min(nflush, n_dn);
-                            const int nm = max(nu, nd);
+                            if (nflush <= min(n_up, n_dn)) {
 #pragma unroll
-                            for (int s = 0; s < (FWD ? TR_NH : 0); ++s) {
-                                if ((s & 3) == 0 && s >= nm) break;
-                                float lo, hi;
-                                unpack2(ACC[s], lo, hi);
-                                if (s < nu) hpc[s * NLOS_TILE] += lo;
-                                if (s < nd) hpc[-(s + 1) * NLOS_TILE] += hi;
+                                for (int s = 0; s < (FWD ? TR_NH : 0); ++s) {
+                                    if ((s & 3) == 0 && s >= nflush) break;
+                                    float lo, hi;
+                                    unpack2(ACC[s], lo, hi);
+                                    hpc[s * NLOS_TILE] += lo;
+                                    hpc[-(s + 1) * NLOS_TILE] += hi;
+                                }
+                            } else {
+                                const int nu = min(nflush, n_up), nd = min(nflush, n_dn);
+                                const int nm = max(nu, nd);
+#pragma unroll
+                                for (int s = 0; s < (FWD ? TR_NH : 0); ++s) {
+                                    if ((s & 3) == 0 && s >= nm) break;
+                                    float lo, hi;
+                                    unpack2(ACC[s], lo, hi);
+                                    if (s < nu) hpc[s * NLOS_TILE] += lo;
+                                    if (s < nd) hpc[-(s + 1) * NLOS_TILE] += hi;
+                                }
                             }
                         }
                     }
