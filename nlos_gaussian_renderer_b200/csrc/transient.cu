@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                     }
                     if (s_lo > s_hi) continue;                                                           // (cannot happen for a listed entry)
                     if (MODE != MODE_COUNT) {
-                        const int nbase = (s_lo / BS) * BS;
+                        const int nbase = s_lo & ~(BS - 1);                                              // bucket is a power of two
                         if (nbase != base) advance(nbase);
                     }
                     const float fRlo = (float)s_lo, fRhi = (float)s_hi;
@@ -812,8 +812,8 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
                        float c_deltaT, float mcut, int mode)
 {
     NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && A >= 1 && A <= 128, "transient: bad sizes");
-    NLOS_REQUIRE(window >= 32 && window % 8 == 0 && bucket >= 1 && 2 * bucket <= window && slice_len > 0,
-                 "transient: bad window/bucket/slice_len");
+    NLOS_REQUIRE(window >= 32 && window % 8 == 0 && bucket >= 1 && (bucket & (bucket - 1)) == 0 && 2 * bucket <= window && slice_len > 0,
+                 "transient: bad window/bucket/slice_len (bucket must be a power of two)");
     NLOS_REQUIRE(mode == MODE_NUM || mode == MODE_ANA, "transient: mode must be 0 (numerical) or 1 (analytic-exact)");
     NLOS_REQUIRE(tiles && records && list && cell_offsets && work, "transient: null pointer");
     NLOS_REQUIRE(((uintptr_t)tiles % 16) == 0 && ((uintptr_t)records % 16) == 0, "transient: tiles/records must be 16-byte aligned");

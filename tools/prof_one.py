@@ -12,12 +12,18 @@ from nlos_gaussian_renderer_b200.transient import TransientRenderer  # noqa: E40
 cfg, mode = sys.argv[1], sys.argv[2]
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 kw = {}
+rows = None
 for a in sys.argv[4:]:
     k, v = a.split("=")
-    kw[k] = int(v)
+    if k == "rows":                       # rows=16: render only the first 16 scan rows of the grid (a slab, as one GPU of a sharded run would)
+        rows = int(v)
+    else:
+        kw[k] = int(v)
 N, Sy, Sx, T, A = scenes.CONFIGS[cfg]
 dev = torch.device("cuda", 0)
 geom = ScanGeometry.wall_grid(Sy, Sx, A=A, device=dev)
+if rows:
+    geom = geom.rows(0, rows)
 ta = scenes.time_axis(T)
 params = scenes.make_gaussians(N, 1000 + list(scenes.CONFIGS).index(cfg) + 1, device=dev)
 r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, **kw)
