@@ -206,11 +206,7 @@ def run_b200(args):
         rnd.prepare(*params)
         e = [ev() for _ in range(4)]
         e[0].record(); Ht = rnd.forward_tiled(); e[1].record()
-        H = geom.untile(Ht)
-        diff = H - target
-        loss = (diff * diff).sum() / fit.numel
-        gH = geom.tile_grad(diff * (2.0 / fit.numel))
-        gH = gH.contiguous()
+        loss, gH = rnd.mse_loss_grad_tiled(Ht, fit.target_tiled, 1.0 / fit.numel)      # fused loss + dL/dH (csrc/loss.cu)
         e[2].record()
         _k = rnd._render_args()
         from nlos_gaussian_renderer_b200 import _lib
@@ -297,7 +293,7 @@ def run_b200(args):
             "clocks": clocks,
             "e2e": {"value": Wb / (ms_e2e / args.steps * 1e-3), "unit": "Gaussian-bin evals/s", "h2d_bytes_per_step": n_bytes,
                     "d2h_bytes_per_step": n_bytes + 4, "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": 8 * args.steps,
+            "gpu_launches": 9 * args.steps,
             "roofline": {"bound": "compute (" + rb["binding_pipe"] + " pipe)", "kernel": f"transient_kernel<{args.mode},bwd>", "achieved": rb["achieved"],
                          "peak": rb["peak"], "unit": "TFLOP/s", "frac": rb["frac"], "traffic": None,
                          "peak_source": f"min(148 SM x 128 FP32 lanes x 2 flop, 148 SM x 16 MUFU/clk x flop-per-MUFU of the algorithmic mix) x {f_mhz} MHz "

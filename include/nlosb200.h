@@ -115,6 +115,19 @@ int nlosb200_render_rays_analytic(const float* ray_origins, const float* ray_dir
                                   int n_rays, int N, int sh_dim, int sh_degree, float scaling_modifier, float sigma_threshold,
                                   int max_sections, float* out, void* stream);
 
+/* ==== fused squared-error loss of the batched fitting step (nlos_helpers.py:280-346 compute_loss, per scan point in the reference; its
+ * batched variant nlos_helpers.py:348-351 is an empty stub): loss += inv_numel * sum (H - target)^2 ; grad_H = 2 inv_numel (H - target)
+ * on the tile-major layout of nlosb200_transient_forward.  n % 4 == 0, 16-byte aligned; loss is ONE double, accumulated (caller zeroes);
+ * grad_H may be NULL. */
+int nlosb200_mse_loss_grad(const float* H, const float* target, long long n, float inv_numel, float* grad_H, double* loss, void* stream);
+
+/* ==== scale-initialisation helper: simple-knn's distCUDA2 (gaussian_model/gaussian_model.py:7-11,202-203; the submodule is pinned at
+ * 60f461f in .SUBMODULES.json but absent from the tree).  out[i] = mean of the squared distances from point i to its 3 nearest OTHER
+ * points (fewer if N < 4; the sum is still divided by 3).  Exact k-NN on a uniform hash grid, no host synchronisation.
+ * workspace: nlosb200_knn_workspace_bytes(N) bytes of device scratch, 16-byte aligned. */
+long long nlosb200_knn_workspace_bytes(int N);
+int nlosb200_knn_dist2(const float* points, int N, float* out, void* workspace, long long workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

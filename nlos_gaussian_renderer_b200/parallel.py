@@ -37,15 +37,26 @@ def gather_transient(H_slab, Sy, tile_y, group=None):
 
 
 class ShardedFitter:
-    """One fitting step on this rank's slab: loss = mean over the GLOBAL grid of (H - target)^2."""
+    """One fitting step on this rank's slab: loss = mean over the GLOBAL grid of (H - target)^2.
+    With a TransientRenderer the step stays in the tile-major layout end to end: forward kernel -> fused loss + dL/dH kernel
+    (csrc/loss.cu) -> backward kernel -> ONE all-reduce of the packed gradients -> per-Gaussian chain."""
 
     def __init__(self, renderer, target_slab, global_numel, group=None):
         self.r, self.target, self.numel, self.group = renderer, target_slab, float(global_numel), group
+        self.fused = hasattr(renderer, "mse_loss_grad_tiled")
+        if self.fused:
+            self.target_tiled = renderer.geom.tile_grad(target_slab).contiguous()      # padding rows zero, as in H
 
     def step(self, means, log_scales, rotations, opacities, features):
         """-> (local loss contribution [tensor], grads tuple summed over all ranks)."""
+        reduce_fn = lambda d: all_reduce_packed(d, self.group)
+        if self.fused:
+            self.r.prepare(means, log_scales, rotations, opacities, features)
+            Ht = self.r.forward_tiled()
+            loss, gH = self.r.mse_loss_grad_tiled(Ht, self.target_tiled, 1.0 / self.numel)
+            return loss, self.r.backward_tiled(gH, reduce_fn=reduce_fn)
         H = self.r.forward(means, log_scales, rotations, opacities, features)
         diff = H - self.target
         loss = (diff * diff).sum() / self.numel
-        grads = self.r.backward(diff * (2.0 / self.numel), reduce_fn=lambda d: all_reduce_packed(d, self.group))
+        grads = self.r.backward(diff * (2.0 / self.numel), reduce_fn=reduce_fn)
         return loss, grads

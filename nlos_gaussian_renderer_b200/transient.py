@@ -135,6 +135,17 @@ class TransientRenderer:
     def backward(self, gH, reduce_fn=None):
         return self.backward_tiled(self.geom.tile_grad(gH), reduce_fn)
 
+    def mse_loss_grad_tiled(self, H_tiled, target_tiled, inv_numel, want_grad=True):
+        """Fused  loss = inv_numel * sum (H - target)^2  and  dL/dH = 2 inv_numel (H - target)  on the tile-major layout
+        (csrc/loss.cu; the batched counterpart of nlos_helpers.py:280-346).  -> (loss 0-d float64 tensor, dL/dH tile-major or None)."""
+        H_tiled, target_tiled = _f32c(H_tiled), _f32c(target_tiled)
+        assert H_tiled.shape == target_tiled.shape
+        loss = torch.zeros((), dtype=torch.float64, device=H_tiled.device)
+        gH = torch.empty_like(H_tiled) if want_grad else None
+        _lib.call("nlosb200_mse_loss_grad", H_tiled.data_ptr(), target_tiled.data_ptr(), H_tiled.numel(), float(inv_numel),
+                  gH.data_ptr() if want_grad else None, loss.data_ptr(), _lib.stream())
+        return loss, gH
+
     def count_work(self):
         """SURVEY.md 8(d) work counters for the prepared scene (dict)."""
         c = torch.zeros(4, dtype=torch.int64, device=self.records.device)

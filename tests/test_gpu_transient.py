@@ -156,3 +156,46 @@ def test_empty_and_degenerate_inputs():
     H = _renderer(geom, ta, "numerical").forward(*z).cpu().numpy().reshape(9, -1)
     H64 = util.oracle_H(geom, ta, z, mode=0, precision="f64")
     assert util.rel_to_max(H, H64) < TOL
+
+
+def test_fused_loss_matches_torch():
+    """csrc/loss.cu on the tile-major layout == torch on [Sy,Sx,T] (ragged grid: padding rows stay out of the loss)."""
+    geom, ta, params = util.small_scene(200, 5, 9, 48, 6, device="cuda")
+    r = _renderer(geom, ta, "numerical")
+    r.prepare(*params)
+    Ht = r.forward_tiled()
+    target = torch.rand(5, 9, 48, device="cuda") * float(Ht.max())
+    numel = 5 * 9 * 48
+    loss, gH = r.mse_loss_grad_tiled(Ht, geom.tile_grad(target), 1.0 / numel)
+    H = geom.untile(Ht)
+    ref_loss = ((H - target).double() ** 2).sum() / numel
+    assert abs(float(loss) - float(ref_loss)) <= 1e-6 * float(ref_loss)
+    ref_g = geom.tile_grad((H - target) * (2.0 / numel))
+    assert torch.allclose(gH, ref_g, rtol=1e-6, atol=0)
+    l2, g2 = r.mse_loss_grad_tiled(Ht, geom.tile_grad(target), 1.0 / numel, want_grad=False)
+    assert g2 is None and float(l2) == float(loss)
+
+
+@pytest.mark.parametrize("mode", ["numerical", "analytic"])
+@pytest.mark.parametrize("scale_mul", [0.08, 0.3, 12.0])
+def test_narrow_and_wide_gaussians(mode, scale_mul):
+    """Gaussians much narrower than a bin (direct / closed-form erf path), around one bin (Gauss-Legendre 4), and wider than the
+    register accumulators (forward excess path, split entries): forward vs the fp64 oracle, backward vs the other decomposition."""
+    N, Sy, Sx, T, A = 120, 4, 8, 256, 6
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=scale_mul, device="cuda")
+    m = 0 if mode == "numerical" else 1
+    r = _renderer(geom, ta, mode)
+    ps = [p.clone().requires_grad_() for p in params]
+    H = render_transient_batch(r, *ps)
+    gH = torch.rand(Sy, Sx, T, generator=torch.Generator().manual_seed(3)).cuda()
+    (H * gH).sum().backward()
+    H64 = util.oracle_H(geom, ta, params, mode=m, precision="f64")
+    if H64.max() > 0:
+        assert util.rel_to_max(H.detach().cpu().numpy().reshape(-1, T), H64) < TOL
+    r2 = _renderer(geom, ta, mode, window=64, bucket=16, slice_len=8)
+    ps2 = [p.clone().requires_grad_() for p in params]
+    H2 = render_transient_batch(r2, *ps2)
+    (H2 * gH).sum().backward()
+    for a, b in zip(ps, ps2):
+        if float(b.grad.abs().max()) > 0:
+            assert util.rel_to_max(a.grad.cpu().numpy(), b.grad.cpu().numpy()) < 5e-5
