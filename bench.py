@@ -152,10 +152,15 @@ def run_reference(args):
     steps, warm = max(args.steps, 1), args.warmup
     # bounded: each step is a sample of scan points sized so the whole run ends within a few minutes
     b = cpu_baseline(args.config, args.mode, args.cpu_points or 4, steps=steps, warmup=min(warm, 1))
-    line = {"impl": "reference", "metric": "Gaussian-bin evals/s (forward; reference backward is a zero stub)", "value": b["value"],
+    (N, Sy, Sx, T, A), _ = scene_for(args.config, max(args.gpus, 1))
+    workload = (f"{args.config}: {N} Gaussians, {Sy}x{Sx} confocal scan ({Sy // max(args.gpus, 1)} rows per GPU), {T} bins, A={A}, "
+                f"{args.mode} integration, forward+backward fitting step")
+    line = {"impl": "reference", "metric": "Gaussian-bin evals/s (forward+backward transient)", "value": b["value"],
             "unit": "Gaussian-bin evals/s", "n_gpus": args.gpus, "steps": steps, "warmup": min(warm, 1),
             "ms_per_step": b["seconds"] * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": {"workload": f"{args.config} (BASELINE.json configs[1]) -- bounded sample", "sample": b["sample"]},
+            "data": "synthetic", "config": {"workload": workload, "sample": b["sample"],
+                                             "note": "the reference's backward is a zero stub (cuda_autograd.py:139-172) and its numerical kernel is its only "
+                                                     "per-bin renderer: the step timed here is its forward; bounded sample of scan points"},
             "cpu_baseline": {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": b["value"], "unit": "Gaussian-bin evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}

@@ -62,22 +62,23 @@ int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, const float
                              long long* cell_offsets, int* tile_items, long long* header, void* stream);
 int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
                              int window, int bucket, const int* chunk_counts_scanned, const long long* cell_offsets, int* list,
-                             long long list_capacity, long long* header, void* stream);
+                             int* list_bins, long long list_capacity, long long* header, void* stream);
 
 /* ---- batched transient H[n_tiles*32, T] and its backward.  mode 0 = numerical (volume_renderer.cu
  * no-occlusion branch :139-182), 1 = analytic-exact per-bin integral.
- * bin k sits at radius t0 + k*dt.  H and dacc are zeroed by the callee.  `work` is int32 scratch [n_tiles] (zeroed by the callee):
+ * bin k sits at radius t0 + k*dt.  H and dacc are zeroed by the callee.  list_bins[i] = klo | khi << 16 is the tile-level shell of
+ * entry i as written by nlosb200_bin_window_fill (T <= 65535).  `work` is int32 scratch [n_tiles] (zeroed by the callee):
  * the per-tile slice counters the persistent CTAs pull work from; slice_len = list entries a warp takes at a time. */
 int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                               const long long* cell_offsets, int* work, float t0, float dt, int T,
+                               const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
                                int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, float* H, void* stream);
 int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                const long long* cell_offsets, int* work, float t0, float dt, int T,
+                                const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
                                 int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, const float* grad_H,
                                 float* dacc, void* stream);
 /* counters uint64 [4]: hit (g,ray) pairs, W_s, sample-evals evaluated, W_b */
 int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                             const long long* cell_offsets, int* work, float t0, float dt, int T,
+                             const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
                              int window, int bucket, int slice_len, float mcut, unsigned long long* counters, void* stream);
 
 /* ==== one-scan-point operators: the reference's pybind module nlos_gaussian_renderer._C ===========================

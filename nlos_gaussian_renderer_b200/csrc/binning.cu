@@ -176,7 +176,8 @@ __global__ void __launch_bounds__(1024) scan_cells_kernel(const int* __restrict_
 __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __restrict__ tiles, int A, const float4* __restrict__ shell, int N,
                                                                  float t0, float inv_dt, int T, int L, int bucket, int n_buckets, int n_chunks,
                                                                  const int* __restrict__ chunk_off, const long long* __restrict__ cell_offsets,
-                                                                 unsigned* __restrict__ list, long long capacity, long long* __restrict__ header)
+                                                                 unsigned* __restrict__ list, unsigned* __restrict__ list_bins, long long capacity,
+                                                                 long long* __restrict__ header)
 {
     __shared__ TilePoints tp;
     __shared__ int wc[BIN_GPT][BIN_THREADS / 32][BIN_MAX_RANGES];
@@ -215,7 +216,10 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __
             if (e >= 0) {
                 size_t cell = (size_t)tile * n_buckets + r;
                 long long pos = cell_offsets[cell] + chunk_off[cell * n_chunks + chunk] + wc[j][warp][r] + __popc(b & lt);
-                if (pos < capacity) list[pos] = (unsigned)g | ((unsigned)e << NLOS_ENTRY_SHIFT);
+                if (pos < capacity) {
+                    list[pos] = (unsigned)g | ((unsigned)e << NLOS_ENTRY_SHIFT);
+                    if (list_bins) list_bins[pos] = (unsigned)lo[j] | ((unsigned)hi[j] << 16);      // the Gaussian's tile-level shell [klo, khi]
+                }
                 else header[2] = 1;
             }
         }
@@ -260,18 +264,19 @@ extern "C" int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, 
 
 extern "C" int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
                                         int window, int bucket, const int* chunk_counts_scanned, const long long* cell_offsets, int* list,
-                                        long long list_capacity, long long* header, void* stream)
+                                        int* list_bins, long long list_capacity, long long* header, void* stream)
 {
     NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0, "bin_window_fill: bad sizes");
     int rc = check_window("bin_window_fill", T, window, bucket, N);
     if (rc) return rc;
     int n_buckets = (T + bucket - 1) / bucket;
     NLOS_REQUIRE(list || list_capacity == 0, "bin_window_fill: null list");
+    NLOS_REQUIRE(!list_bins || T <= 65535, "bin_window_fill: list_bins packs two 16-bit bins (T=%d)", T);
     int n_chunks = (N + BIN_CHUNK - 1) / BIN_CHUNK;
     float inv_dt = 1.0f / dt;
     shell_fill_kernel<<<dim3(n_chunks, n_tiles), BIN_THREADS, 0, (cudaStream_t)stream>>>(
         tiles, A, reinterpret_cast<const float4*>(shell), N, t0, inv_dt, T, window - bucket, bucket, n_buckets, n_chunks, chunk_counts_scanned,
-        cell_offsets, reinterpret_cast<unsigned*>(list), list_capacity, header);
+        cell_offsets, reinterpret_cast<unsigned*>(list), reinterpret_cast<unsigned*>(list_bins), list_capacity, header);
     NLOS_CHECK_LAUNCH("shell_fill_kernel");
     return 0;
 }

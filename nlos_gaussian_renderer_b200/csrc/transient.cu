@@ -57,6 +57,7 @@ struct TransientParams {
     const float* records;
     int N;
     const unsigned* list;            // entries g | e << NLOS_ENTRY_SHIFT, tile-major, ordered by bucket
+    const unsigned* list_bins;       // per entry: tile-level shell klo | khi << 16 (binning.cu:shell_fill_kernel)
     const long long* cell_offsets;   // [n_tiles*n_buckets + 1]
     int* work;                       // [n_tiles] next slice of every tile's entry list (zeroed before the launch)
     float t0, dt, inv_dt;
@@ -99,15 +100,21 @@ __device__ __forceinline__ float hi_of(f32x2 v) { float a, b; unpack2(v, a, b); 
 // up bin kc+s has tau = tc + s dt, down bin kc-1-s has tau = tc - dt - s dt.
 __device__ __forceinline__ void stream_moments(f32x2 A, f32x2 B, f32x2 C, float nf, float tc, float dt, float& S0, float& S1, float& S2)
 {
-    float Au, Ad, Bu, Bd, Cu, Cd;
-    unpack2(A, Au, Ad); unpack2(B, Bu, Bd); unpack2(C, Cu, Cd);
-    const float M1u = fmaf(nf, Au, -Bu), M1d = fmaf(nf, Ad, -Bd);                                  // sum x s
-    const float M2u = fmaf(nf, fmaf(nf, Au, -2.0f * Bu), fmaf(2.0f, Cu, -Bu));                     // sum x s^2
-    const float M2d = fmaf(nf, fmaf(nf, Ad, -2.0f * Bd), fmaf(2.0f, Cd, -Bd));
+    // evaluated on the packed {up, down} halves, then the two halves are added
+    const f32x2 n2 = pack2(nf, nf), neg1 = pack2(-1.0f, -1.0f), two = pack2(2.0f, 2.0f);
+    const f32x2 nB = mul2(B, neg1);
+    const f32x2 M1 = fma2(n2, A, nB);                                                       // sum x s
+    const f32x2 M2 = fma2(n2, fma2(n2, A, add2(nB, nB)), fma2(two, C, nB));                 // sum x s^2
     const float td = tc - dt, dt2 = dt * dt;
-    S0 += Au + Ad;
-    S1 += fmaf(tc, Au, dt * M1u) + fmaf(td, Ad, -dt * M1d);
-    S2 += fmaf(tc * tc, Au, fmaf(2.0f * tc * dt, M1u, dt2 * M2u)) + fmaf(td * td, Ad, fmaf(-2.0f * td * dt, M1d, dt2 * M2d));
+    const f32x2 T1 = pack2(tc, td), DT = pack2(dt, -dt);
+    const f32x2 T2 = mul2(T1, T1), TT = mul2(mul2(T1, DT), two);
+    const f32x2 s1 = fma2(T1, A, mul2(DT, M1));
+    const f32x2 s2 = fma2(T2, A, fma2(TT, M1, mul2(pack2(dt2, dt2), M2)));
+    float a0, a1, b0, b1, c0, c1;
+    unpack2(A, a0, a1); unpack2(s1, b0, b1); unpack2(s2, c0, c1);
+    S0 += a0 + a1;
+    S1 += b0 + b1;
+    S2 += c0 + c1;
 }
 
 template <int MODE, bool BWD>
@@ -253,7 +260,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
 
             // ---- TMA ring over the list slice
             const int n_batches = (n + TR_RING - 1) / TR_RING;
-            unsigned ent_next = 0, ent_cur = 0;
+            unsigned ent_next = 0, ent_cur = 0, bins_next = 0, bins_cur = 0;
             auto issue = [&](int b, unsigned r) {
                 const int stage = (int)(r & 1u);
                 const int cnt = min(TR_RING, n - b * TR_RING);
@@ -265,6 +272,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                 ent_next = 0;
                 if (lane < cnt) {
                     ent_next = P.list[beg + b * TR_RING + lane];
+                    bins_next = P.list_bins[beg + b * TR_RING + lane];
                     bulk_g2s(ring + (stage * TR_RING + lane) * NLOS_REC_FLOATS,
                              P.records + (size_t)(ent_next & ((1u << NLOS_ENTRY_SHIFT) - 1u)) * NLOS_REC_FLOATS, NLOS_REC_FLOATS * 4u, &bar[stage]);
                 }
@@ -272,6 +280,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
             issue(0, rb);
             for (int b = 0; b < n_batches; ++b, ++rb) {
                 ent_cur = ent_next;
+                bins_cur = bins_next;
                 if (b + 1 < n_batches) issue(b + 1, rb + 1);   // (overwrites ent_next; ent_cur keeps this batch's entries)
                 mbar_wait(&bar[rb & 1u], (rb >> 1) & 1u);
                 const int cnt = min(TR_RING, n - b * TR_RING);
@@ -283,19 +292,13 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                     const float M00 = v1.x, M01 = v1.y, M02 = v1.z, M10 = v1.w, M11 = v2.x, M12 = v2.y, M20 = v2.z, M21 = v2.w, M22 = v3.x;
                     const float opalb = v0.w * v4.w;
                     const float cx = v0.x - ox, cy = v0.y - oy, cz = v0.z - oz;                             // mu - o
-                    // ---- the tile-level shell of this Gaussian, bit-identical to binning.cu:shell_bins (warp min/max over the scan points)
+                    // ---- the tile-level shell [klo, khi] of this Gaussian comes with the list entry (binning.cu:shell_bins)
                     int s_lo, s_hi;
                     bool split, lo_exact, hi_exact, force_slow;
-                    float d2;
+                    const float d2 = fmaf(cx, cx, fmaf(cy, cy, cz * cz));
                     {
-                        d2 = __fadd_rn(__fadd_rn(__fmul_rn(cx, cx), __fmul_rn(cy, cy)), __fmul_rn(cz, cz));
-                        const unsigned umin = __reduce_min_sync(0xffffffffu, valid ? __float_as_uint(d2) : 0x7f800000u);
-                        const unsigned umax = __reduce_max_sync(0xffffffffu, valid ? __float_as_uint(d2) : 0u);
-                        const float rlo = __fsub_rn(__fsqrt_rn(__uint_as_float(umin)), v5.x), rhi = __fadd_rn(__fsqrt_rn(__uint_as_float(umax)), v5.x);
-                        const float klo_f = floorf(__fadd_rn(__fmul_rn(__fsub_rn(rlo, t0), inv_dt), 0.5f));
-                        const float khi_f = floorf(__fadd_rn(__fmul_rn(__fsub_rn(rhi, t0), inv_dt), 0.5f));
-                        const int klo_t = klo_f < 0.0f ? 0 : (klo_f > (float)(T - 1) ? T : (int)klo_f);
-                        const int khi_t = khi_f < 0.0f ? -1 : (khi_f > (float)(T - 1) ? T - 1 : (int)khi_f);
+                        const unsigned bw = __shfl_sync(0xffffffffu, bins_cur, q);
+                        const int klo_t = (int)(bw & 0xffffu), khi_t = (int)(bw >> 16);
                         s_lo = klo_t + esub * L;                                                         // this entry's sub-interval
                         s_hi = min(khi_t, s_lo + L - 1);
                         split = khi_t - klo_t + 1 > L;                                                   // the Gaussian has more than one entry
@@ -314,6 +317,8 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                     float gax = 0.f, gay = 0.f, gaz = 0.f;                                                  // dL/da
                     float g00 = 0.f, g01 = 0.f, g02 = 0.f, g10 = 0.f, g11 = 0.f, g12 = 0.f, g20 = 0.f, g21 = 0.f, g22 = 0.f;   // sum dL/db (x) d
                     float gwa = 0.f;                                                                        // dL/d(op*alb)
+                    // numerical backward: the same sums with ray 0 / ray 1 of an iteration in the two halves of packed registers
+                    f32x2 pga[3] = {0ull, 0ull, 0ull}, pg[9] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull}, pgwa = 0ull;
                     bool act = valid && (MODE == MODE_COUNT || opalb > 0.f);
                     float D = 0.f;
                     if (act) {
@@ -452,6 +457,30 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                             g00 = fmaf(bxw, dx, g00); g01 = fmaf(bxw, dy, g01); g02 = fmaf(bxw, dz, g02);
                             g10 = fmaf(byw, dx, g10); g11 = fmaf(byw, dy, g11); g12 = fmaf(byw, dz, g12);
                             g20 = fmaf(bzw, dx, g20); g21 = fmaf(bzw, dy, g21); g22 = fmaf(bzw, dz, g22);
+                        };
+                        // the chain rule of the two rays of an iteration in packed fp32x2 (a ray outside the cut arrives with S = 0)
+                        auto ray_chain2 = [&](const float* tha, const float* pha, const float* thb_, const float* phb_, f32x2 rsp, f32x2 S0, f32x2 S1,
+                                              f32x2 S2) {
+                            const f32x2 sth = pack2(tha[TH_SIN], thb_[TH_SIN]), cth = pack2(tha[TH_COS], thb_[TH_COS]);
+                            const f32x2 sph = pack2(pha[PH_SIN], phb_[PH_SIN]), cph = pack2(pha[PH_COS], phb_[PH_COS]);
+                            const f32x2 dx = mul2(sth, cph), dy = mul2(sth, sph);
+                            const f32x2 bx = fma2(pack2(M00, M00), dx, fma2(pack2(M01, M01), dy, mul2(pack2(M02, M02), cth)));
+                            const f32x2 by = fma2(pack2(M10, M10), dx, fma2(pack2(M11, M11), dy, mul2(pack2(M12, M12), cth)));
+                            const f32x2 bz = fma2(pack2(M20, M20), dx, fma2(pack2(M21, M21), dy, mul2(pack2(M22, M22), cth)));
+                            const f32x2 Dv = pack2(D, D);
+                            const f32x2 px = fma2(rsp, bx, fma2(Dv, bx, pack2(ax, ax))), py = fma2(rsp, by, fma2(Dv, by, pack2(ay, ay))),
+                                        pz = fma2(rsp, bz, fma2(Dv, bz, pack2(az, az)));                     // perp
+                            const f32x2 ux = fma2(S1, bx, mul2(S0, px)), uy = fma2(S1, by, mul2(S0, py)), uz = fma2(S1, bz, mul2(S0, pz));
+                            const f32x2 rsu = add2(Dv, rsp);
+                            const f32x2 vx = fma2(rsu, ux, fma2(S2, bx, mul2(S1, px))), vy = fma2(rsu, uy, fma2(S2, by, mul2(S1, py))),
+                                        vz = fma2(rsu, uz, fma2(S2, bz, mul2(S1, pz)));
+                            const f32x2 nw = mul2(sth, pack2(-opalb, -opalb));
+                            pgwa = fma2(sth, S0, pgwa);
+                            pga[0] = fma2(nw, ux, pga[0]); pga[1] = fma2(nw, uy, pga[1]); pga[2] = fma2(nw, uz, pga[2]);
+                            const f32x2 bxw = mul2(nw, vx), byw = mul2(nw, vy), bzw = mul2(nw, vz);
+                            pg[0] = fma2(bxw, dx, pg[0]); pg[1] = fma2(bxw, dy, pg[1]); pg[2] = fma2(bxw, cth, pg[2]);
+                            pg[3] = fma2(byw, dx, pg[3]); pg[4] = fma2(byw, dy, pg[4]); pg[5] = fma2(byw, cth, pg[5]);
+                            pg[6] = fma2(bzw, dx, pg[6]); pg[7] = fma2(bzw, dy, pg[7]); pg[8] = fma2(bzw, cth, pg[8]);
                         };
                         // ---- seeds of one stream at the centre bin.  tc = t(kc) + node offset - r*
                         //      E = {e(kc), e(kc-1)} * weight ; G = {e(kc+1)/e(kc), e(kc-2)/e(kc-1)} ; q = ratio of consecutive ratios
@@ -617,10 +646,8 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         seed(R0.gam, R0.al, R0.tc, ok0 ? (BWD ? 1.0f : opalb * R0.sth) : 0.f, E0, G0, q0);
                                         seed(R1.gam, R1.al, R1.tc, ok1 ? (BWD ? 1.0f : opalb * R1.sth) : 0.f, E1, G1, q1);
                                         run2(E0, G0, q0, E1, G1, q1, nst, R0.tc, R1.tc, S0a, S1a, S2a, S0b, S1b, S2b);
-                                        if (BWD) {
-                                            if (ok0) ray_chain(th0p, ph0p, R0.rsp, S0a, S1a, S2a);
-                                            if (ok1) ray_chain(th1p, ph1p, R1.rsp, S0b, S1b, S2b);
-                                        }
+                                        if (BWD)
+                                            ray_chain2(th0p, ph0p, th1p, ph1p, pack2(R0.rsp, R1.rsp), pack2(S0a, S0b), pack2(S1a, S1b), pack2(S2a, S2b));
                                     }
                                 }
                                 // ---- 3. slow loop: direct evaluation of whole rays (slow_full) or of the bins beyond the register accumulators
@@ -730,6 +757,13 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                         }
                     }
                     if (GRAD) {
+                        if (MODE == MODE_NUM) {
+                            gax += lo_of(pga[0]) + hi_of(pga[0]); gay += lo_of(pga[1]) + hi_of(pga[1]); gaz += lo_of(pga[2]) + hi_of(pga[2]);
+                            g00 += lo_of(pg[0]) + hi_of(pg[0]); g01 += lo_of(pg[1]) + hi_of(pg[1]); g02 += lo_of(pg[2]) + hi_of(pg[2]);
+                            g10 += lo_of(pg[3]) + hi_of(pg[3]); g11 += lo_of(pg[4]) + hi_of(pg[4]); g12 += lo_of(pg[5]) + hi_of(pg[5]);
+                            g20 += lo_of(pg[6]) + hi_of(pg[6]); g21 += lo_of(pg[7]) + hi_of(pg[7]); g22 += lo_of(pg[8]) + hi_of(pg[8]);
+                            gwa += lo_of(pgwa) + hi_of(pgwa);
+                        }
                         // a = M (o - mu) = -M c :  dL/dM += dL/da (x) (o - mu) ;  dL/dmu = -M^T dL/da
                         float o[13];
                         o[0] = fmaf(-gax, cx, g00); o[1] = fmaf(-gax, cy, g01); o[2] = fmaf(-gax, cz, g02);
@@ -808,6 +842,7 @@ static int launch_transient(const TransientParams& P, cudaStream_t s, const char
 }
 
 static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                       const int* list_bins,
                        const long long* cell_offsets, int* work, float t0, float dt, int T, int window, int bucket, int slice_len,
                        float c_deltaT, float mcut, int mode)
 {
@@ -815,9 +850,11 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
     NLOS_REQUIRE(window >= 32 && window % 8 == 0 && bucket >= 1 && (bucket & (bucket - 1)) == 0 && 2 * bucket <= window && slice_len > 0,
                  "transient: bad window/bucket/slice_len (bucket must be a power of two)");
     NLOS_REQUIRE(mode == MODE_NUM || mode == MODE_ANA, "transient: mode must be 0 (numerical) or 1 (analytic-exact)");
-    NLOS_REQUIRE(tiles && records && list && cell_offsets && work, "transient: null pointer");
+    NLOS_REQUIRE(tiles && records && list && list_bins && cell_offsets && work, "transient: null pointer");
+    NLOS_REQUIRE(T <= 65535, "transient: T=%d > 65535", T);
     NLOS_REQUIRE(((uintptr_t)tiles % 16) == 0 && ((uintptr_t)records % 16) == 0, "transient: tiles/records must be 16-byte aligned");
     P.tiles = tiles; P.n_tiles = n_tiles; P.A = A; P.records = records; P.N = N; P.list = reinterpret_cast<const unsigned*>(list);
+    P.list_bins = reinterpret_cast<const unsigned*>(list_bins);
     P.cell_offsets = cell_offsets; P.work = work;
     P.t0 = t0; P.dt = dt; P.inv_dt = 1.0f / dt; P.T = T; P.window = window; P.bucket = bucket; P.n_buckets = (T + bucket - 1) / bucket;
     P.slice_len = slice_len; P.flush_scale = mode == MODE_NUM ? c_deltaT : 1.0f; P.mcut2 = mcut * mcut;
@@ -828,11 +865,11 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
 extern "C" int nlosb200_transient_warps_per_block(void) { return TR_WPB; }
 
 extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                          const long long* cell_offsets, int* work, float t0, float dt, int T,
+                                          const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
                                           int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, float* H, void* stream)
 {
     TransientParams P;
-    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, cell_offsets, work, t0, dt, T, window, bucket, slice_len, c_deltaT, mcut,
+    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, cell_offsets, work, t0, dt, T, window, bucket, slice_len, c_deltaT, mcut,
                          mode);
     if (rc) return rc;
     NLOS_REQUIRE(H, "transient_forward: null H");
@@ -845,12 +882,12 @@ extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A
 }
 
 extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                           const long long* cell_offsets, int* work, float t0, float dt, int T,
+                                           const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
                                            int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, const float* grad_H,
                                            float* dacc, void* stream)
 {
     TransientParams P;
-    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, cell_offsets, work, t0, dt, T, window, bucket, slice_len, c_deltaT, mcut,
+    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, cell_offsets, work, t0, dt, T, window, bucket, slice_len, c_deltaT, mcut,
                          mode);
     if (rc) return rc;
     NLOS_REQUIRE(grad_H && dacc, "transient_backward: null pointer");
@@ -865,11 +902,11 @@ extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int 
 
 // work counters of SURVEY.md 8(d): counters[0] hit (g,ray) pairs, [1] W_s, [2] sample-evals this library evaluates, [3] W_b
 extern "C" int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                        const long long* cell_offsets, int* work, float t0, float dt, int T,
+                                        const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
                                         int window, int bucket, int slice_len, float mcut, unsigned long long* counters, void* stream)
 {
     TransientParams P;
-    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, cell_offsets, work, t0, dt, T, window, bucket, slice_len, 1.0f, mcut,
+    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, cell_offsets, work, t0, dt, T, window, bucket, slice_len, 1.0f, mcut,
                          MODE_NUM);
     if (rc) return rc;
     NLOS_REQUIRE(counters, "transient_count: null counters");

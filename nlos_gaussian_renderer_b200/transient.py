@@ -96,13 +96,14 @@ class TransientRenderer:
         self.last_total = total
         if self._list is None or self._list.numel() < total:
             self._list = torch.empty(max(int(total * 1.25), 1024), dtype=torch.int32, device=means.device)
+            self._list_bins = torch.empty_like(self._list)                # per entry: shell klo | khi << 16
         _lib.call("nlosb200_bin_window_fill", *self._bin_args(), self.chunk_counts.data_ptr(), self.cell_offsets.data_ptr(),
-                  self._list.data_ptr(), self._list.numel(), self.header.data_ptr(), st)
+                  self._list.data_ptr(), self._list_bins.data_ptr(), self._list.numel(), self.header.data_ptr(), st)
 
     def _render_args(self):
         g = self.geom
         return (g.tiles().data_ptr(), g.n_tiles, g.A, self.records.data_ptr(), self._N, self._list.data_ptr(),
-                self.cell_offsets.data_ptr(), self.work.data_ptr(), self.t0, self.dt, self.T, self.window, self.bucket, self._slice)
+                self._list_bins.data_ptr(), self.cell_offsets.data_ptr(), self.work.data_ptr(), self.t0, self.dt, self.T, self.window, self.bucket, self._slice)
 
     def forward_tiled(self):
         """-> H [n_tiles*32, T] in tile-major scan order (after prepare())."""
