@@ -594,57 +594,79 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                     const float* const th0p = thb + (b0 >> 3) * 96;
                                     const float* const ph0p = phb + (b0 & 7) * 128;
                                     float S0a = 0.f, S1a = 0.f, S2a = 0.f, S0b = 0.f, S1b = 0.f, S2b = 0.f;
+                                    // ---- two rays per iteration.  A missing second ray, or a ray outside the cut, rides along as a zero-weight
+                                    //      copy of its partner (finite seeds, no contribution)
+                                    const bool has1 = mask != 0;
+                                    const int b1 = has1 ? __ffs(mask) - 1 : b0;
+                                    mask &= mask - 1;
+                                    const float* const th1p = thb + (b1 >> 3) * 96;
+                                    const float* const ph1p = phb + (b1 & 7) * 128;
+                                    Ray R0, R1;
+                                    ray_setup2(th0p, ph0p, th1p, ph1p, R0, R1);
+                                    const bool ok0 = R0.ok, ok1 = has1 && R1.ok;
+                                    if (!(ok0 || ok1)) continue;
+                                    if (!ok0) { R0.gam = R1.gam; R0.al = R1.al; R0.tc = R1.tc; R0.hh = R1.hh; }
+                                    if (!ok1) { R1.gam = R0.gam; R1.al = R0.al; R1.tc = R0.tc; R1.hh = R0.hh; }
+                                    const unsigned bits = (ok0 ? 1u << b0 : 0u) | (ok1 ? 1u << b1 : 0u);
+                                    const float off = (MODE == MODE_ANA) ? 0.5f : 0.0f;                  // analytic: the nodes sit up to half a bin off
+                                    const float at0 = fabsf(R0.tc) + off * dt, at1 = fabsf(R1.tc) + off * dt;
+                                    const float hx = fmaxf(fmaf(at0, inv_dt, R0.hh), fmaf(at1, inv_dt, R1.hh));   // steps - 1 that reach the cut
+                                    const float Lmin = fminf(fmaf(R0.gam * at0, at0, R0.al), fmaf(R1.gam * at1, at1, R1.al));
+                                    const float gpm = -fminf(R0.gam, R1.gam) * dt2;                      // 0.72 / (sigma in bins)^2 of the narrower ray
+                                    // seeds representable, recurrence well conditioned (analytic: quadrature accurate)
+                                    if (!(Lmin > -100.f && gpm < (MODE == MODE_ANA ? 2.0f : 6.0f))) { slow_full |= bits; continue; }
+                                    if (FWD && hx >= (float)(TR_NH - 1)) slow_excess |= bits;
+                                    const int nst = min(min((int)hx + 1, n_lim), FWD ? TR_NH : 0x7fffffff);
+                                    const float w0 = ok0 ? (BWD ? 1.0f : opalb * R0.sth) : 0.f, w1 = ok1 ? (BWD ? 1.0f : opalb * R1.sth) : 0.f;
                                     if (MODE == MODE_ANA) {
-                                        // ---- analytic-exact: one ray; Gauss-Legendre nodes +-xn of the unit bin are its two streams
-                                        //      GL2 when the ray is wider than 3 bins (sigma), else GL4 (two passes)
-                                        Ray R;
-                                        ray_setup(th0p, ph0p, R);
-                                        if (!R.ok) continue;
-                                        const float gp = -R.gam * dt2;                                   // 0.72 / (sigma in bins)^2
-                                        const float tfar = fabsf(R.tc) + 0.5f * dt;
-                                        if (!(gp < 2.0f && fmaf(R.gam * tfar, tfar, R.al) > -100.f)) { slow_full |= 1u << b0; continue; }
-                                        const float hx = R.hh + fabsf(R.tc) * inv_dt + 0.5f;
-                                        if (FWD && hx >= (float)(TR_NH - 1)) slow_excess |= 1u << b0;
-                                        const int nst = min(min((int)hx + 1, n_lim), FWD ? TR_NH : 0x7fffffff);
-                                        const float wbase = (BWD ? 1.0f : opalb * R.sth) * dt;
-                                        const int npass = gp <= 0.08f ? 1 : 2;
+                                        // ---- analytic-exact: every bin is integrated with Gauss-Legendre nodes, each node one stream of the same
+                                        //      recurrence.  kind 0: GL2 (both rays wider than 3 bins), 1: GL3 (wider than 1 bin; the two centre nodes
+                                        //      of the pair share one pass), 2: GL4.  Passes: kind 0: A+-, B+- ; kind 1: A+-, B+-, (A0,B0) ;
+                                        //      kind 2: A+-, A+-, B+-, B+-.  Without a second ray: A's passes only.
+                                        const int kind = gpm <= 0.08f ? 0 : (gpm <= 0.72f ? 1 : 2);
+                                        const bool two = ok0 && ok1;
+                                        // ray A is the valid one when only one is
+                                        const Ray& RA = ok0 ? R0 : R1;
+                                        const Ray& RB = R1;
+                                        const float wA = (ok0 ? w0 : w1) * dt, wB = w1 * dt;
+                                        const int npass = two ? kind + 2 : (kind == 0 ? 1 : 2);
+                                        float SA0 = 0.f, SA1 = 0.f, SA2 = 0.f, SB0 = 0.f, SB1 = 0.f, SB2 = 0.f;
 #pragma unroll 1
                                         for (int ps = 0; ps < npass; ++ps) {
-                                            const float xn = (npass == 1 ? 0.28867513459481287f : (ps == 0 ? 0.16999052179242816f : 0.43056815579702626f)) * dt;
-                                            const float wn = (npass == 1 ? 0.5f : (ps == 0 ? 0.32607257743127305f : 0.17392742256872692f)) * wbase;
+                                            // pass -> (ray of stream 0, ray of stream 1, node offset, node weight)
+                                            const bool mixed = kind == 1 && ps == (two ? 2 : 1);                       // centre nodes
+                                            const bool onB = two && !mixed && (kind == 2 ? ps >= 2 : ps == 1);
+                                            float xn, wn;
+                                            if (kind == 0) { xn = 0.28867513459481287f; wn = 0.5f; }
+                                            else if (kind == 1) { xn = mixed ? 0.f : 0.3872983346207417f; wn = mixed ? 0.4444444444444444f : 0.2777777777777778f; }
+                                            else { xn = (ps & 1) ? 0.43056815579702626f : 0.16999052179242816f; wn = (ps & 1) ? 0.17392742256872692f : 0.32607257743127305f; }
+                                            xn *= dt;
+                                            const float g0 = onB ? RB.gam : RA.gam, a0 = onB ? RB.al : RA.al, t0s = (onB ? RB.tc : RA.tc) + xn;
+                                            const bool s1B = onB || (mixed && two);
+                                            const float g1 = s1B ? RB.gam : RA.gam, a1 = s1B ? RB.al : RA.al, t1s = (s1B ? RB.tc : RA.tc) - xn;
+                                            const float ws0 = (onB ? wB : wA) * wn, ws1 = (mixed && !two) ? 0.f : (s1B ? wB : wA) * wn;
                                             f32x2 E0, G0, E1, G1;
                                             float q0, q1;
-                                            seed(R.gam, R.al, R.tc + xn, wn, E0, G0, q0);
-                                            seed(R.gam, R.al, R.tc - xn, wn, E1, G1, q1);
-                                            run2(E0, G0, q0, E1, G1, q1, nst, R.tc + xn, R.tc - xn, S0a, S1a, S2a, S0a, S1a, S2a);
+                                            seed(g0, a0, t0s, ws0, E0, G0, q0);
+                                            seed(g1, a1, t1s, ws1, E1, G1, q1);
+                                            float m00 = 0.f, m01 = 0.f, m02 = 0.f, m10 = 0.f, m11 = 0.f, m12 = 0.f;
+                                            run2(E0, G0, q0, E1, G1, q1, nst, t0s, t1s, m00, m01, m02, m10, m11, m12);
+                                            if (BWD) {
+                                                if (onB) { SB0 += m00; SB1 += m01; SB2 += m02; } else { SA0 += m00; SA1 += m01; SA2 += m02; }
+                                                if (s1B) { SB0 += m10; SB1 += m11; SB2 += m12; } else { SA0 += m10; SA1 += m11; SA2 += m12; }
+                                            }
                                         }
-                                        if (BWD) ray_chain(th0p, ph0p, R.rsp, S0a, S1a, S2a);
+                                        if (BWD) {
+                                            // (ray A is R1 when R0 missed the cut: its moments then belong to the second half)
+                                            if (ok0) ray_chain2(th0p, ph0p, th1p, ph1p, pack2(R0.rsp, R1.rsp), pack2(SA0, SB0), pack2(SA1, SB1), pack2(SA2, SB2));
+                                            else ray_chain2(th0p, ph0p, th1p, ph1p, pack2(R0.rsp, R1.rsp), pack2(0.f, SA0), pack2(0.f, SA1), pack2(0.f, SA2));
+                                        }
                                     } else {
-                                        // ---- numerical mode: two rays = two streams.  A missing second ray, or a ray outside the cut, rides along
-                                        //      as a zero-weight copy of its partner (finite seeds, no contribution)
-                                        const bool has1 = mask != 0;
-                                        const int b1 = has1 ? __ffs(mask) - 1 : b0;
-                                        mask &= mask - 1;
-                                        const float* const th1p = thb + (b1 >> 3) * 96;
-                                        const float* const ph1p = phb + (b1 & 7) * 128;
-                                        Ray R0, R1;
-                                        ray_setup2(th0p, ph0p, th1p, ph1p, R0, R1);
-                                        const bool ok0 = R0.ok, ok1 = has1 && R1.ok;
-                                        if (!(ok0 || ok1)) continue;
-                                        if (!ok0) { R0.gam = R1.gam; R0.al = R1.al; R0.tc = R1.tc; R0.hh = R1.hh; }
-                                        if (!ok1) { R1.gam = R0.gam; R1.al = R0.al; R1.tc = R0.tc; R1.hh = R0.hh; }
-                                        const float hx0 = R0.hh + fabsf(R0.tc) * inv_dt, hx1 = R1.hh + fabsf(R1.tc) * inv_dt;   // steps - 1 that reach the cut
-                                        const float L0 = fmaf(R0.gam * R0.tc, R0.tc, R0.al), L1 = fmaf(R1.gam * R1.tc, R1.tc, R1.al);
-                                        const unsigned bits = (ok0 ? 1u << b0 : 0u) | (ok1 ? 1u << b1 : 0u);
-                                        // seeds representable, recurrence well conditioned
-                                        if (!(fminf(L0, L1) > -100.f && fminf(R0.gam, R1.gam) * dt2 > -6.f)) { slow_full |= bits; continue; }
-                                        const float hx = fmaxf(hx0, hx1);
-                                        if (FWD && hx >= (float)(TR_NH - 1)) slow_excess |= bits;
-                                        const int nst = min(min((int)hx + 1, n_lim), FWD ? TR_NH : 0x7fffffff);
+                                        // ---- numerical mode: the two rays are the two streams
                                         f32x2 E0, G0, E1, G1;
                                         float q0, q1;
-                                        seed(R0.gam, R0.al, R0.tc, ok0 ? (BWD ? 1.0f : opalb * R0.sth) : 0.f, E0, G0, q0);
-                                        seed(R1.gam, R1.al, R1.tc, ok1 ? (BWD ? 1.0f : opalb * R1.sth) : 0.f, E1, G1, q1);
+                                        seed(R0.gam, R0.al, R0.tc, w0, E0, G0, q0);
+                                        seed(R1.gam, R1.al, R1.tc, w1, E1, G1, q1);
                                         run2(E0, G0, q0, E1, G1, q1, nst, R0.tc, R1.tc, S0a, S1a, S2a, S0b, S1b, S2b);
                                         if (BWD)
                                             ray_chain2(th0p, ph0p, th1p, ph1p, pack2(R0.rsp, R1.rsp), pack2(S0a, S0b), pack2(S1a, S1b), pack2(S2a, S2b));
@@ -757,7 +779,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                         }
                     }
                     if (GRAD) {
-                        if (MODE == MODE_NUM) {
+                        {
                             gax += lo_of(pga[0]) + hi_of(pga[0]); gay += lo_of(pga[1]) + hi_of(pga[1]); gaz += lo_of(pga[2]) + hi_of(pga[2]);
                             g00 += lo_of(pg[0]) + hi_of(pg[0]); g01 += lo_of(pg[1]) + hi_of(pg[1]); g02 += lo_of(pg[2]) + hi_of(pg[2]);
                             g10 += lo_of(pg[3]) + hi_of(pg[3]); g11 += lo_of(pg[4]) + hi_of(pg[4]); g12 += lo_of(pg[5]) + hi_of(pg[5]);

@@ -4,7 +4,7 @@ import torch
 
 import oracle
 from nlos_gaussian_renderer_b200 import scenes
-from nlos_gaussian_renderer_b200.geometry import ScanGeometry
+from nlos_gaussian_renderer_b200.geometry import ScanGeometry  # noqa: F401 (re-exported for the tests)
 
 
 def small_scene(N=150, Sy=5, Sx=9, T=48, A=6, seed=7, scale_mul=1.0, device="cpu"):
