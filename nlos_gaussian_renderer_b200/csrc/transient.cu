@@ -549,37 +549,43 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                 //         the column only and the z slab on the row only (same operations, same order: bit-exact decisions)
                                 unsigned mask = 0;
                                 const int ni = min(4, i1 - ib + 1), nj = min(8, j1 - jb + 1);
-                                float xymn[8], xymx[8];
+                                // (columns in two halves of 4: footprints are rarely wider, the second half is skipped by a branch)
 #pragma unroll
-                                for (int jj = 0; jj < 8; ++jj) {
-                                    xymn[jj] = INFINITY; xymx[jj] = -INFINITY;
-                                    if (jj < nj) {
-                                        const float icp = phb[jj * 128 + PH_ICOS], isp = phb[jj * 128 + PH_ISIN];
-                                        const float tx0 = lox * icp, tx1 = hix * icp, ty0 = loy * isp, ty1 = hiy * isp;
-                                        xymn[jj] = fmaxf(fminf(tx0, tx1), fminf(ty0, ty1));
-                                        xymx[jj] = fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1));
-                                    }
-                                }
+                                for (int jh = 0; jh < 8; jh += 4) {
+                                    if (jh < nj) {
+                                        float xymn[4], xymx[4];
 #pragma unroll
-                                for (int ii = 0; ii < 4; ++ii) {
-                                    if (ii < ni) {
-                                        const float tth = thb[ii * 96 + TH_TAN];
-                                        const float tz0 = loz * tth, tz1 = hiz * tth;
-                                        const float zmn = fminf(tz0, tz1), zmx = fmaxf(tz0, tz1);
+                                        for (int jj = 0; jj < 4; ++jj) {
+                                            xymn[jj] = INFINITY; xymx[jj] = -INFINITY;
+                                            if (jh + jj < nj) {
+                                                const float icp = phb[(jh + jj) * 128 + PH_ICOS], isp = phb[(jh + jj) * 128 + PH_ISIN];
+                                                const float tx0 = lox * icp, tx1 = hix * icp, ty0 = loy * isp, ty1 = hiy * isp;
+                                                xymn[jj] = fmaxf(fminf(tx0, tx1), fminf(ty0, ty1));
+                                                xymx[jj] = fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1));
+                                            }
+                                        }
 #pragma unroll
-                                        for (int jj = 0; jj < 8; ++jj) {
-                                            const float tmin = fmaxf(xymn[jj], zmn);
-                                            const float tmax = fminf(xymx[jj], zmx);
-                                            const bool hit = (tmax >= tmin) && (tmax >= 0.f);
-                                            mask |= (hit ? 1u : 0u) << (ii * 8 + jj);
-                                            if (MODE == MODE_COUNT && hit) {
-                                                // slab interval stretched about its midpoint by 5.3/3 (t = t'/sin(theta))
-                                                const float ist = 1.0f / thb[ii * 96 + TH_SIN];
-                                                const float mid = 0.5f * (tmin + tmax) * ist, half = 0.5f * (tmax - tmin) * ist * (5.3f / 3.0f);
-                                                const int ka = clamp_ceil((mid - half - t0) * inv_dt, s_lo, s_hi + 1),
-                                                          kb = clamp_floor((mid + half - t0) * inv_dt, s_lo - 1, s_hi);
-                                                c_hits += (r_in <= mid && mid < r_out) ? 1 : 0;
-                                                if (kb >= ka) { c_ws += kb - ka + 1; wb_lo = min(wb_lo, ka); wb_hi = max(wb_hi, kb); }
+                                        for (int ii = 0; ii < 4; ++ii) {
+                                            if (ii < ni) {
+                                                const float tth = thb[ii * 96 + TH_TAN];
+                                                const float tz0 = loz * tth, tz1 = hiz * tth;
+                                                const float zmn = fminf(tz0, tz1), zmx = fmaxf(tz0, tz1);
+#pragma unroll
+                                                for (int jj = 0; jj < 4; ++jj) {
+                                                    const float tmin = fmaxf(xymn[jj], zmn);
+                                                    const float tmax = fminf(xymx[jj], zmx);
+                                                    const bool hit = (tmax >= tmin) && (tmax >= 0.f);
+                                                    mask |= (hit ? 1u : 0u) << (ii * 8 + jh + jj);
+                                                    if (MODE == MODE_COUNT && hit) {
+                                                        // slab interval stretched about its midpoint by 5.3/3 (t = t'/sin(theta))
+                                                        const float ist = 1.0f / thb[ii * 96 + TH_SIN];
+                                                        const float mid = 0.5f * (tmin + tmax) * ist, half = 0.5f * (tmax - tmin) * ist * (5.3f / 3.0f);
+                                                        const int ka = clamp_ceil((mid - half - t0) * inv_dt, s_lo, s_hi + 1),
+                                                                  kb = clamp_floor((mid + half - t0) * inv_dt, s_lo - 1, s_hi);
+                                                        c_hits += (r_in <= mid && mid < r_out) ? 1 : 0;
+                                                        if (kb >= ka) { c_ws += kb - ka + 1; wb_lo = min(wb_lo, ka); wb_hi = max(wb_hi, kb); }
+                                                    }
+                                                }
                                             }
                                         }
                                     }
