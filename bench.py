@@ -90,6 +90,22 @@ def scene_for(cfg, n_gpus):
     return (N, Sy * n_gpus, Sx, T, A), seed
 
 
+
+def ncu_traffic(cfg, mode):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the backward kernel, per launch, from the committed `ncu --set full` capture of the same
+    workload (profiles/r01_f_ncu_raw_<cfg>_<mode>.txt); None when there is no capture for this workload."""
+    path = os.path.join(ROOT, "profiles", f"r01_f_ncu_raw_{cfg}_{mode}.txt")
+    if not os.path.exists(path):
+        return None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot = 0.0
+    for ln in open(path):
+        if ln.startswith("dram__bytes_read.sum") or ln.startswith("dram__bytes_write.sum"):
+            u = ln.split("[")[1].split("]")[0]
+            tot += float(ln.split("|")[2]) * unit.get(u, 1.0)          # column 2 = transient_kernel<mode, bwd>
+    return tot or None
+
+
 # ----------------------------------------------------------------------------------------------------------------
 def cpu_baseline(cfg, mode, n_points, steps=1, warmup=0):
     """Times the reference's own CUDA-kernel source compiled for the host cores (oracle/_ref, kind "reference") when that
@@ -300,7 +316,8 @@ def run_b200(args):
                     "d2h_bytes_per_step": n_bytes + 4, "ms_per_step": ms_e2e / args.steps},
             "gpu_launches": 9 * args.steps,
             "roofline": {"bound": "compute (" + rb["binding_pipe"] + " pipe)", "kernel": f"transient_kernel<{args.mode},bwd>", "achieved": rb["achieved"],
-                         "peak": rb["peak"], "unit": "TFLOP/s", "frac": rb["frac"], "traffic": None,
+                         "peak": rb["peak"], "unit": "TFLOP/s", "frac": rb["frac"],
+                         "traffic": ncu_traffic(args.config, args.mode) if world == 1 else None,
                          "peak_source": f"min(148 SM x 128 FP32 lanes x 2 flop, 148 SM x 16 MUFU/clk x flop-per-MUFU of the algorithmic mix) x {f_mhz} MHz "
                                         "(SM clock sampled during the run; SURVEY.md 8d); MEASURED_PEAKS.json holds only HBM and bf16 tensor peaks, "
                                         "neither binds this kernel (DRAM traffic ~45 MB per launch)",
