@@ -801,18 +801,29 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                         o[10] = -(M01 * gax + M11 * gay + M21 * gaz);
                         o[11] = -(M02 * gax + M12 * gay + M22 * gaz);
                         o[12] = gwa;
+                        // transposing butterfly: 16 shuffles reduce the 13 sums over the warp (instead of 13 x 5); after the step with
+                        // lane-xor 16/8/4/2 each lane keeps half of its slots, so slot index = lane bits 4..1 and lanes 2i, 2i+1 both end
+                        // with the total of slot i
+                        float v[16];
 #pragma unroll
-                        for (int i = 0; i < 13; ++i) o[i] = warp_sum(o[i]);
-                        const int g = (int)(ent & ((1u << NLOS_ENTRY_SHIFT) - 1u));
-                        if (lane < 14) {
-                            // slots: 0..8 dM, 9..11 dmu, 12 dop = alb * d(op*alb), 13 dalb = op * d(op*alb)
-                            float val = 0.f;
+                        for (int i = 0; i < 16; ++i) v[i] = i < 13 ? o[i] : 0.f;
 #pragma unroll
-                            for (int i = 0; i < 12; ++i) val = (lane == i) ? o[i] : val;
-                            if (lane == 12) val = o[12] * v4.w;
-                            if (lane == 13) val = o[12] * v0.w;
-                            if (val != 0.f) atomicAdd(P.dacc + (size_t)g * NLOS_GRAD_FLOATS + lane, val);
+                        for (int half = 8, bit = 16; half >= 1; half >>= 1, bit >>= 1) {
+                            const bool up = lane & bit;
+#pragma unroll
+                            for (int i = 0; i < half; ++i) {
+                                const float send = up ? v[i] : v[i + half], keep = up ? v[i + half] : v[i];
+                                v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+                            }
                         }
+                        float val = v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+                        const int slot = lane >> 1;
+                        const int g = (int)(ent & ((1u << NLOS_ENTRY_SHIFT) - 1u));
+                        // slots: 0..8 dM, 9..11 dmu, 12 dop = alb * d(op*alb), 13 dalb = op * d(op*alb) (the two lanes of slot 12 write these)
+                        int dst = slot;
+                        bool wr = !(lane & 1) && slot < 12;
+                        if (slot == 12) { val *= (lane & 1) ? v0.w : v4.w; dst = 12 + (lane & 1); wr = true; }
+                        if (wr && val != 0.f) atomicAdd(P.dacc + (size_t)g * NLOS_GRAD_FLOATS + dst, val);
                     }
                 }
                 __syncwarp();
