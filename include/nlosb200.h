@@ -122,6 +122,13 @@ int nlosb200_render_rays_analytic(const float* ray_origins, const float* ray_dir
  * grad_H may be NULL. */
 int nlosb200_mse_loss_grad(const float* H, const float* target, long long n, float inv_numel, float* grad_H, double* loss, void* stream);
 
+/* ==== fused multi-tensor Adam step of the Gaussian parameter groups (GaussianModel.training_setup, gaussian_model/gaussian_model.py:223-249:
+ * one torch.optim.Adam over mu / f_dc / f_rest / opacity / scaling / rotation with per-group lr, eps = 1e-15, no weight decay; stepped at
+ * main.py:161,213).  params / grads / exp_avg / exp_avg_sq are HOST arrays of n_tensors (<= 8) DEVICE pointers, sizes / lrs HOST arrays;
+ * step = 1, 2, ... selects the bias corrections.  Same operation order as torch.optim.Adam's single-tensor path. */
+int nlosb200_adam_step(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg, float* const* exp_avg_sq,
+                       const long long* sizes, const float* lrs, float beta1, float beta2, float eps, int step, void* stream);
+
 /* ==== scale-initialisation helper: simple-knn's distCUDA2 (gaussian_model/gaussian_model.py:7-11,202-203; the submodule is pinned at
  * 60f461f in .SUBMODULES.json but absent from the tree).  out[i] = mean of the squared distances from point i to its 3 nearest OTHER
  * points (fewer if N < 4; the sum is still divided by 3).  Exact k-NN on a uniform hash grid, no host synchronisation.
