@@ -129,6 +129,13 @@ int nlosb200_mse_loss_grad(const float* H, const float* target, long long n, flo
 int nlosb200_adam_step(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg, float* const* exp_avg_sq,
                        const long long* sizes, const float* lrs, float beta1, float beta2, float eps, int step, void* stream);
 
+/* ==== dense evaluation of the mixture at arbitrary points: density = sum_g pdf_g sigmoid(o_g), rho_density = sum_g pdf_g sigmoid(o_g) albedo_g over
+ * ALL Gaussians (GaussianModel.estimate_rho_w_no_occlusion(out_separately=True), gaussian_model/gaussian_model.py:346-364, as used by the volume
+ * evaluation nlos_helpers.py:40-69 gaussian2volume; pdf in the CUDA renderer's arithmetic, include/cuda_utils.cuh:124-151).  records from
+ * nlosb200_preprocess (+ nlosb200_compat_albedo for a camera-dependent albedo).  Outputs [n_points], overwritten. */
+int nlosb200_evaluate_points(const float* points, long long n_points, const float* records, int N, float* density, float* rho_density,
+                             void* stream);
+
 /* ==== scale-initialisation helper: simple-knn's distCUDA2 (gaussian_model/gaussian_model.py:7-11,202-203; the submodule is pinned at
  * 60f461f in .SUBMODULES.json but absent from the tree).  out[i] = mean of the squared distances from point i to its 3 nearest OTHER
  * points (fewer if N < 4; the sum is still divided by 3).  Exact k-NN on a uniform hash grid, no host synchronisation.

@@ -155,3 +155,32 @@ def render_rays_analytic(ray_origins, ray_directions, t_min, t_max, gaussian_fil
               gaussian_opacities.data_ptr(), feats.data_ptr(), camera_pos.data_ptr(), n_rays, N, feats.shape[1], int(active_sh_degree),
               float(scaling_modifier), float(sigma_threshold), ms, out.data_ptr(), _lib.stream())
     return out
+
+
+def evaluate_points(points, gaussian_means, gaussian_scales, gaussian_rotations, gaussian_opacities, gaussian_features, camera_pos=None,
+                    active_sh_degree=0, scaling_modifier=1.0):
+    """Dense evaluation at `points` [Na,3] -> (rho_density [Na], density [Na]): sums over ALL Gaussians, the quantities
+    GaussianModel.estimate_rho_w_no_occlusion(..., out_separately=True) returns (gaussian_model/gaussian_model.py:346-364) and
+    gaussian2volume samples (nlos_helpers.py:40-69), with the CUDA renderer's pdf arithmetic (include/cuda_utils.cuh:124-151).
+    camera_pos None -> degree-0 albedo; else the view-dependent albedo of that position (volume_renderer.cu:107-111)."""
+    for t, n in ((points, "points"), (gaussian_means, "gaussian_means"), (gaussian_scales, "gaussian_scales"),
+                 (gaussian_rotations, "gaussian_rotations"), (gaussian_opacities, "gaussian_opacities"), (gaussian_features, "gaussian_features")):
+        _check(t, n)
+    N, dev = gaussian_means.shape[0], gaussian_means.device
+    L = _lib.lib()
+    feats = gaussian_features.reshape(N, -1) if N else gaussian_features.reshape(0, 1)
+    records = _aligned(max(N, 1) * L.nlosb200_record_floats(), torch.float32, dev, 128)
+    st = _lib.stream()
+    if N:
+        _lib.call("nlosb200_preprocess", gaussian_means.data_ptr(), gaussian_scales.data_ptr(), gaussian_rotations.data_ptr(),
+                  gaussian_opacities.data_ptr(), feats.data_ptr(), N, feats.shape[1], float(scaling_modifier), 3.0, 0.0, records.data_ptr(),
+                  None, None, st)
+        if camera_pos is not None:
+            _check(camera_pos, "camera_pos")
+            _lib.call("nlosb200_compat_albedo", gaussian_means.data_ptr(), feats.data_ptr(), camera_pos.data_ptr(), N, feats.shape[1],
+                      int(active_sh_degree), records.data_ptr(), st)
+    Na = points.shape[0]
+    density = torch.zeros(Na, dtype=torch.float32, device=dev)
+    rho_density = torch.zeros(Na, dtype=torch.float32, device=dev)
+    _lib.call("nlosb200_evaluate_points", points.data_ptr(), Na, records.data_ptr(), N, density.data_ptr(), rho_density.data_ptr(), st)
+    return rho_density, density

@@ -95,3 +95,19 @@ def render_rays(ray_o, ray_d, t, mask, means, log_scales, rots, opac, feats, c, 
     alive = torch.cumprod(alive.to(torch.int64), 1).bool()
     z = torch.zeros_like(density)
     return torch.where(alive, Tr * wa, z), torch.where(alive, density, z), torch.where(alive, Tr, z)
+
+
+def evaluate_points(x, means, log_scales, rots, opac, feats, mod=1.0, chunk=512):
+    """Dense sums over ALL Gaussians at points x [Na,3] -> (rho_density, density), the quantities of
+    GaussianModel.estimate_rho_w_no_occlusion(out_separately=True) (gaussian_model/gaussian_model.py:346-364) with the CUDA renderer's
+    pdf (include/cuda_utils.cuh:124-151) and degree-0 albedo."""
+    M, op, alb = activate(means, log_scales, rots, opac, feats, mod)
+    dens = torch.zeros(x.shape[0], dtype=x.dtype)
+    rho = torch.zeros(x.shape[0], dtype=x.dtype)
+    for g0 in range(0, means.shape[0], chunk):
+        sl = slice(g0, g0 + chunk)
+        loc = torch.einsum("gij,gnj->gni", M[sl], x[None] - means[sl][:, None])
+        pdf = torch.exp(-0.5 * (loc * loc).sum(-1))
+        dens += (pdf * op[sl, None]).sum(0)
+        rho += (pdf * (op[sl] * alb[sl])[:, None]).sum(0)
+    return rho, dens
