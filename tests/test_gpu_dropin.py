@@ -85,3 +85,38 @@ def test_batched_slice_equals_per_scan_point_operator(mode_occl):
         ref = (hist * geom.vp_y ** 2).detach().cpu().numpy()
         got = H.reshape(Sy * Sx, T)[p].cpu().numpy()
         assert util.rel_to_max(got, ref) < 1e-4
+
+
+@pytest.mark.parametrize("occl", [True, False])
+def test_occluded_batch_equals_per_scan_point_loop(occl):
+    """render_transient_batch_occluded (one operator call per chunk of scan points) == the reference's loop of CUDARenderModule.forward over
+    the scan points (main.py:198-203) times vp_y^2 (nlos_helpers.py:275-276), values and parameter gradients."""
+    from nlos_gaussian_renderer_b200.dropin.cuda_autograd import CUDARenderModule
+    from nlos_gaussian_renderer_b200.occluded import render_transient_batch_occluded
+    N, Sy, Sx, T, A = 120, 2, 3, 48, 6
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=3.0, device="cuda")
+    params = list(params)
+    params[3] = params[3] + 3.0                                      # opaque enough for the transmittance to matter
+    r0, r1 = ta["start"] * ta["c"] * ta["deltaT"], ta["end"] * ta["c"] * ta["deltaT"]
+    t_samples = torch.linspace(r0, r1, T, device="cuda")
+    pa = [p.clone().requires_grad_() for p in params]
+    H = render_transient_batch_occluded(geom, t_samples, *pa, ta["c"], ta["deltaT"], use_occlusion=occl, chunk_scan_points=4)
+    assert tuple(H.shape) == (Sy, Sx, T)
+    wgt = torch.linspace(0.5, 1.5, Sy * Sx * T, device="cuda").reshape(Sy, Sx, T)
+    (H * wgt).sum().backward()
+    gm = FakeGaussianModel(*params)
+    module = CUDARenderModule()
+    rows = []
+    for p in range(Sy * Sx):
+        th, ph = geom.theta_range[p].tolist(), geom.phi_range[p].tolist()
+        _, hist = module(gm, geom.scan_o[p], tuple(th), tuple(ph), (r0, r1), A, A, T, ta["c"], ta["deltaT"], 1.0, occl, "netf")
+        rows.append(hist * geom.vp_y ** 2)
+    Href = torch.stack(rows).reshape(Sy, Sx, T)
+    (Href * wgt).sum().backward()
+    assert util.rel_to_max(H.detach().cpu().numpy(), Href.detach().cpu().numpy()) < 1e-5
+    if occl:                                                          # occlusion changes the result on this scene
+        Hn = render_transient_batch_occluded(geom, t_samples, *params, ta["c"], ta["deltaT"], use_occlusion=False)
+        assert util.rel_to_max(Hn.cpu().numpy(), H.detach().cpu().numpy()) > 1e-3
+    for a, b in zip(pa, (gm._mu, gm._scaling, gm._rotation, gm._opacity, gm._features_dc)):
+        assert float(b.grad.abs().max()) > 0
+        assert util.rel_to_max(a.grad.reshape(-1).cpu().numpy(), b.grad.reshape(-1).cpu().numpy()) < 1e-4
