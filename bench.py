@@ -32,6 +32,8 @@ def parse():
     ap.add_argument("--config", default="cfg2")
     ap.add_argument("--mode", default="analytic", choices=["analytic", "numerical"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak (default): every rank renders its own Sy-row slab of a (Sy*N) x Sx grid; strong: the config's grid is split over the ranks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-points", type=int, default=0, help="scan points in the CPU baseline sample (0 = auto)")
     return ap.parse_args()
@@ -83,11 +85,11 @@ class ClockSampler:
         return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def scene_for(cfg, n_gpus):
+def scene_for(cfg, n_gpus, strong=False):
     from nlos_gaussian_renderer_b200 import scenes
     N, Sy, Sx, T, A = scenes.CONFIGS[cfg]
     seed = 1000 + list(scenes.CONFIGS).index(cfg) + 1
-    return (N, Sy * n_gpus, Sx, T, A), seed
+    return (N, Sy if strong else Sy * n_gpus, Sx, T, A), seed
 
 
 
@@ -168,12 +170,12 @@ def run_reference(args):
     steps, warm = max(args.steps, 1), args.warmup
     # bounded: each step is a sample of scan points sized so the whole run ends within a few minutes
     b = cpu_baseline(args.config, args.mode, args.cpu_points or 4, steps=steps, warmup=min(warm, 1))
-    (N, Sy, Sx, T, A), _ = scene_for(args.config, max(args.gpus, 1))
+    (N, Sy, Sx, T, A), _ = scene_for(args.config, max(args.gpus, 1), args.scaling == "strong")
     workload = (f"{args.config}: {N} Gaussians, {Sy}x{Sx} confocal scan ({Sy // max(args.gpus, 1)} rows per GPU), {T} bins, A={A}, "
                 f"{args.mode} integration, forward+backward fitting step")
     line = {"impl": "reference", "metric": "Gaussian-bin evals/s (forward+backward transient)", "value": b["value"],
             "unit": "Gaussian-bin evals/s", "n_gpus": args.gpus, "steps": steps, "warmup": min(warm, 1),
-            "ms_per_step": b["seconds"] * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "ms_per_step": b["seconds"] * 1e3, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": {"workload": workload, "sample": b["sample"],
                                              "note": "the reference's backward is a zero stub (cuda_autograd.py:139-172) and its numerical kernel is its only "
                                                      "per-bin renderer: the step timed here is its forward; bounded sample of scan points"},
@@ -199,7 +201,7 @@ def run_b200(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    shape, seed = scene_for(args.config, world)
+    shape, seed = scene_for(args.config, world, args.scaling == "strong")
     N, Sy, Sx, T, A = shape
     ta = scenes.time_axis(T)
     full = ScanGeometry.wall_grid(Sy, Sx, A=A)
@@ -304,7 +306,7 @@ def run_b200(args):
         line = {
             "metric": "Gaussian-bin evals/s (forward+backward transient)", "value": Wb / (ms_step * 1e-3), "unit": "Gaussian-bin evals/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"{args.config}: {N} Gaussians, {Sy}x{Sx} confocal scan ({Sy // world} rows per GPU), {T} bins, A={A}, "
                                    f"{args.mode} integration, forward+backward fitting step", "parallelism": f"scan-slab x{world}",
                        "l2": "256 MB memset between steps (inside the timed region)", "mode": args.mode,
