@@ -28,10 +28,10 @@
 //      summed over all rays of the pair and merged into the shared window ONCE per pair;
 //      backward: the three moments sum_k w_k e_k tau^n (n = 0,1,2) per ray from running prefix sums (A += w e; B += A;
 //      C += B), chain rule to dL/dM, dL/dmu, dL/dop, dL/dalb per lane, ONE warp-shuffle reduction per entry, 14 REDs;
-//   4. the analytic-exact mode integrates every bin with Gauss-Legendre nodes (2 or 4 by the ray's width in bins;
-//      <= 1e-5 of the peak, far below the 1e-4 parity tolerance): each node is one more recurrence stream on the same
-//      registers.  Rays narrower than 0.6 bins, or whose seeds are not representable, take the closed-form erf path
-//      (analytic) / the direct 1-MUFU-per-bin path (numerical).
+//   4. the analytic-exact mode integrates every bin by replacing the bin's box with a moment-matched mixture of 1 or 2
+//      Gaussians (rays wider than 3 bins / 1 bin; <= 1.3e-5 of the peak, far below the 1e-4 parity tolerance) or with
+//      GL4 nodes: each node is one more recurrence stream on the same registers.  Rays narrower than 0.6 bins, or whose
+//      seeds are not representable, take the closed-form erf path (analytic) / the direct 1-MUFU-per-bin path (numerical).
 #include "common.cuh"
 #include "../../include/nlosb200.h"
 
@@ -625,26 +625,44 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                     const int nst = min(min((int)hx + 1, n_lim), FWD ? TR_NH : 0x7fffffff);
                                     const float w0 = ok0 ? (BWD ? 1.0f : opalb * R0.sth) : 0.f, w1 = ok1 ? (BWD ? 1.0f : opalb * R1.sth) : 0.f;
                                     if (MODE == MODE_ANA) {
-                                        // ---- analytic-exact: every bin is integrated with Gauss-Legendre nodes, each node one stream of the same
-                                        //      recurrence.  kind 0: GL2 (both rays wider than 3 bins), 1: GL3 (wider than 1 bin; the two centre nodes
-                                        //      of the pair share one pass), 2: GL4.  Passes: kind 0: A+-, B+- ; kind 1: A+-, B+-, (A0,B0) ;
-                                        //      kind 2: A+-, A+-, B+-, B+-.  Without a second ray: A's passes only.
+                                        // ---- analytic-exact: the bin integral is the Gaussian convolved with the unit box of the bin.  The box is
+                                        //      replaced by a mixture of Gaussians with the same low moments, so every node is ONE stream of the same
+                                        //      recurrence on a Gaussian whose variance is inflated by s2 (precision C -> C / u, u = 1 + C s2,
+                                        //      amplitude u^-1/2):
+                                        //        kind 0 (both rays wider than 3 bins): 1 node, s2 = dt^2/12 (moments to order 3, <= 1.3e-5 of the peak);
+                                        //                the two rays of the pair are the two streams of ONE pass
+                                        //        kind 1 (wider than 1 bin): 2 nodes +-x, x^4 = dt^4/240, s2 = dt^2/12 - x^2 (moments to order 5: the
+                                        //                accuracy of GL3, <= 7e-6 of the peak, at the cost of GL2).  Passes: A+-, B+-
+                                        //        kind 2: plain GL4 (s2 = 0).  Passes: A+-, A+-, B+-, B+-.
+                                        //      Without a second ray: A's passes only.
                                         const int kind = gpm <= 0.08f ? 0 : (gpm <= 0.72f ? 1 : 2);
                                         const bool two = ok0 && ok1;
+                                        const float s2k = kind == 0 ? dt2 * (1.0f / 12.0f) : (kind == 1 ? dt2 * 0.018783611f : 0.f);
+                                        float iu0, iu1;
+                                        {
+                                            // x = C s2 <= 0.019: 1/u and log2(u) by their series (errors < 2e-7)
+                                            const float x0 = R0.gam * (s2k / KG), x1 = R1.gam * (s2k / KG);
+                                            iu0 = fmaf(-x0, fmaf(-x0, 1.0f - x0, 1.0f), 1.0f);
+                                            iu1 = fmaf(-x1, fmaf(-x1, 1.0f - x1, 1.0f), 1.0f);
+                                            R0.al = fmaf(-0.5f * LOG2E_F * x0, fmaf(-x0, fmaf(-x0, 1.0f / 3.0f, 0.5f), 1.0f), R0.al);
+                                            R1.al = fmaf(-0.5f * LOG2E_F * x1, fmaf(-x1, fmaf(-x1, 1.0f / 3.0f, 0.5f), 1.0f), R1.al);
+                                            R0.gam *= iu0;
+                                            R1.gam *= iu1;
+                                        }
                                         // ray A is the valid one when only one is
                                         const Ray& RA = ok0 ? R0 : R1;
                                         const Ray& RB = R1;
                                         const float wA = (ok0 ? w0 : w1) * dt, wB = w1 * dt;
-                                        const int npass = two ? kind + 2 : (kind == 0 ? 1 : 2);
+                                        const int npass = kind == 0 ? 1 : (two ? 2 * kind : kind);
                                         float SA0 = 0.f, SA1 = 0.f, SA2 = 0.f, SB0 = 0.f, SB1 = 0.f, SB2 = 0.f;
 #pragma unroll 1
                                         for (int ps = 0; ps < npass; ++ps) {
                                             // pass -> (ray of stream 0, ray of stream 1, node offset, node weight)
-                                            const bool mixed = kind == 1 && ps == (two ? 2 : 1);                       // centre nodes
+                                            const bool mixed = kind == 0;                                              // stream 0 = ray A, stream 1 = ray B
                                             const bool onB = two && !mixed && (kind == 2 ? ps >= 2 : ps == 1);
                                             float xn, wn;
-                                            if (kind == 0) { xn = 0.28867513459481287f; wn = 0.5f; }
-                                            else if (kind == 1) { xn = mixed ? 0.f : 0.3872983346207417f; wn = mixed ? 0.4444444444444444f : 0.2777777777777778f; }
+                                            if (kind == 0) { xn = 0.f; wn = 1.0f; }
+                                            else if (kind == 1) { xn = 0.25406644f; wn = 0.5f; }
                                             else { xn = (ps & 1) ? 0.43056815579702626f : 0.16999052179242816f; wn = (ps & 1) ? 0.17392742256872692f : 0.32607257743127305f; }
                                             xn *= dt;
                                             const float g0 = onB ? RB.gam : RA.gam, a0 = onB ? RB.al : RA.al, t0s = (onB ? RB.tc : RA.tc) + xn;
@@ -663,6 +681,11 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                             }
                                         }
                                         if (BWD) {
+                                            // chain rule through the inflation:  d ln e' = -d(m2min)/2 - tau^2 dC / (2 u^2) + C tau dr* / u - s2 dC / (2 u),
+                                            // i.e. the moments the plain chain rule expects are  S0, S1 / u, S2 / u^2 + S0 s2 / u
+                                            const float iuA = ok0 ? iu0 : iu1, iuB = iu1;
+                                            SA2 = fmaf(SA2 * iuA, iuA, SA0 * (s2k * iuA)); SA1 *= iuA;
+                                            SB2 = fmaf(SB2 * iuB, iuB, SB0 * (s2k * iuB)); SB1 *= iuB;
                                             // (ray A is R1 when R0 missed the cut: its moments then belong to the second half)
                                             if (ok0) ray_chain2(th0p, ph0p, th1p, ph1p, pack2(R0.rsp, R1.rsp), pack2(SA0, SB0), pack2(SA1, SB1), pack2(SA2, SB2));
                                             else ray_chain2(th0p, ph0p, th1p, ph1p, pack2(R0.rsp, R1.rsp), pack2(0.f, SA0), pack2(0.f, SA1), pack2(0.f, SA2));
