@@ -29,7 +29,7 @@
 //      backward: the three moments sum_k w_k e_k tau^n (n = 0,1,2) per ray from running prefix sums (A += w e; B += A;
 //      C += B), chain rule to dL/dM, dL/dmu, dL/dop, dL/dalb per lane, ONE warp-shuffle reduction per entry, 14 REDs;
 //   4. the analytic-exact mode integrates every bin by replacing the bin's box with a moment-matched mixture of 1 or 2
-//      Gaussians (rays wider than 3 bins / 1 bin; <= 1.3e-5 of the peak, far below the 1e-4 parity tolerance) or with
+//      Gaussians (rays wider than 2.5 / 0.8 bins; <= 2.6e-5 of the peak per ray, below the 1e-4 parity tolerance) or with
 //      GL4 nodes: each node is one more recurrence stream on the same registers.  Rays narrower than 0.6 bins, or whose
 //      seeds are not representable, take the closed-form erf path (analytic) / the direct 1-MUFU-per-bin path (numerical).
 #include "common.cuh"
@@ -48,6 +48,13 @@ using namespace nlos;
 #define LOG2E_F 1.4426950408889634f
 #define SQRT_PI_2 1.2533141373155001f
 #define NO_BASE (-0x40000000)
+// analytic mode: gpm = 0.72 / (ray width in bins)^2 up to which the 1-node / 2-node moment-matched mixtures are used
+#ifndef TR_GPM_K0
+#define TR_GPM_K0 0.115f   // >= 2.5 bins
+#endif
+#ifndef TR_GPM_K1
+#define TR_GPM_K1 1.125f   // >= 0.8 bins
+#endif
 
 enum { MODE_NUM = 0, MODE_ANA = 1, MODE_COUNT = 2 };
 
@@ -264,10 +271,10 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
             auto issue = [&](int b, unsigned r) {
                 const int stage = (int)(r & 1u);
                 const int cnt = min(TR_RING, n - b * TR_RING);
-                if (lane == 0) {
-                    fence_proxy_async();
-                    mbar_arrive_expect_tx(&bar[stage], (uint32_t)cnt * NLOS_REC_FLOATS * 4u);
-                }
+                // (no proxy fence: the stage is only ever READ through the generic proxy, and those reads were consumed before the
+                //  __syncwarp below; fence.proxy.async is MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC, i.e. it would wait for this warp's
+                //  outstanding gradient / histogram REDs every 4 entries -- 15 % of the backward's stall samples)
+                if (lane == 0) mbar_arrive_expect_tx(&bar[stage], (uint32_t)cnt * NLOS_REC_FLOATS * 4u);
                 __syncwarp();
                 ent_next = 0;
                 if (lane < cnt) {
@@ -629,18 +636,18 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         //      replaced by a mixture of Gaussians with the same low moments, so every node is ONE stream of the same
                                         //      recurrence on a Gaussian whose variance is inflated by s2 (precision C -> C / u, u = 1 + C s2,
                                         //      amplitude u^-1/2):
-                                        //        kind 0 (both rays wider than 3 bins): 1 node, s2 = dt^2/12 (moments to order 3, <= 1.3e-5 of the peak);
+                                        //        kind 0 (both rays wider than 2.5 bins): 1 node, s2 = dt^2/12 (moments to order 3, <= 2.6e-5 of the peak);
                                         //                the two rays of the pair are the two streams of ONE pass
-                                        //        kind 1 (wider than 1 bin): 2 nodes +-x, x^4 = dt^4/240, s2 = dt^2/12 - x^2 (moments to order 5: the
-                                        //                accuracy of GL3, <= 7e-6 of the peak, at the cost of GL2).  Passes: A+-, B+-
+                                        //        kind 1 (wider than 0.8 bins): 2 nodes +-x, x^4 = dt^4/240, s2 = dt^2/12 - x^2 (moments to order 5: the
+                                        //                accuracy of GL3, <= 2.5e-5 of the peak, at the cost of GL2).  Passes: A+-, B+-
                                         //        kind 2: plain GL4 (s2 = 0).  Passes: A+-, A+-, B+-, B+-.
                                         //      Without a second ray: A's passes only.
-                                        const int kind = gpm <= 0.08f ? 0 : (gpm <= 0.72f ? 1 : 2);
+                                        const int kind = gpm <= TR_GPM_K0 ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);
                                         const bool two = ok0 && ok1;
                                         const float s2k = kind == 0 ? dt2 * (1.0f / 12.0f) : (kind == 1 ? dt2 * 0.018783611f : 0.f);
                                         float iu0, iu1;
                                         {
-                                            // x = C s2 <= 0.019: 1/u and log2(u) by their series (errors < 2e-7)
+                                            // x = C s2 <= 0.03: 1/u and log2(u) by their series (errors < 1e-6)
                                             const float x0 = R0.gam * (s2k / KG), x1 = R1.gam * (s2k / KG);
                                             iu0 = fmaf(-x0, fmaf(-x0, 1.0f - x0, 1.0f), 1.0f);
                                             iu1 = fmaf(-x1, fmaf(-x1, 1.0f - x1, 1.0f), 1.0f);
