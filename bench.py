@@ -94,11 +94,13 @@ def scene_for(cfg, n_gpus, strong=False):
 
 
 def ncu_traffic(cfg, mode):
-    """dram__bytes_read.sum + dram__bytes_write.sum of the backward kernel, per launch, from the committed `ncu --set full` capture of the same
-    workload (profiles/r01_f_ncu_raw_<cfg>_<mode>.txt); None when there is no capture for this workload."""
-    path = os.path.join(ROOT, "profiles", f"r01_f_ncu_raw_{cfg}_{mode}.txt")
-    if not os.path.exists(path):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the backward kernel, per launch, from the latest committed `ncu --set full` capture of
+    the same workload (profiles/r01_<x>_ncu_raw_<cfg>_<mode>.txt, the last in name order); None when there is no capture for this workload."""
+    import glob
+    found = sorted(glob.glob(os.path.join(ROOT, "profiles", f"r[0-9][0-9]_?_ncu_raw_{cfg}_{mode}.txt")))
+    if not found:
         return None
+    path = found[-1]
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     tot = 0.0
     for ln in open(path):

@@ -71,10 +71,12 @@ def test_forward_slice_and_range_invariance():
         assert util.rel_to_max(H.cpu().numpy(), ref.cpu().numpy()) < 5e-6
 
 
-@pytest.mark.parametrize("mode", ["numerical", "analytic"])
-def test_backward_matches_autograd(mode):
+@pytest.mark.parametrize("mode,scale_mul", [("numerical", 2.0), ("analytic", 2.0), ("analytic", 0.6), ("analytic", 1.2), ("analytic", 5.0)])
+def test_backward_matches_autograd(mode, scale_mul):
+    """scale_mul 2.0: ray widths 1.5-6 bins; the analytic sweep covers the closed-form erf / GL4 rays (0.6: 0.45-1.8 bins), the 2-node
+    mixture (1.2: 0.9-3.6 bins) and the 1-node mixture (5.0: 3.8-15 bins) with the chain rule through the variance inflation."""
     N, Sy, Sx, T, A = 120, 5, 9, 40, 5
-    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=2.0, device="cuda")
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=scale_mul, device="cuda")
     m = 0 if mode == "numerical" else 1
     gen = torch.Generator().manual_seed(5)
     gH = torch.rand(Sy, Sx, T, generator=gen)
@@ -179,7 +181,7 @@ def test_fused_loss_matches_torch():
 @pytest.mark.parametrize("mode", ["numerical", "analytic"])
 @pytest.mark.parametrize("scale_mul", [0.08, 0.3, 12.0])
 def test_narrow_and_wide_gaussians(mode, scale_mul):
-    """Gaussians much narrower than a bin (direct / closed-form erf path), around one bin (Gauss-Legendre 4), and wider than the
+    """Gaussians much narrower than a bin (direct / closed-form erf path), around one bin (GL4 nodes / 2-component mixture), and wider than the
     register accumulators (forward excess path, split entries): forward vs the fp64 oracle, backward vs the other decomposition."""
     N, Sy, Sx, T, A = 120, 4, 8, 256, 6
     geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=scale_mul, device="cuda")

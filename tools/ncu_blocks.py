@@ -7,7 +7,7 @@ from collections import Counter
 rows=list(csv.reader(open(sys.argv[1])))
 which=int(sys.argv[2]); thr=float(sys.argv[3]) if len(sys.argv)>3 else 0.006
 hdr=[i for i,r in enumerate(rows) if r and r[0]=='Address']
-H=rows[hdr[0]]; ci={n:i for i,n in enumerate(H)}
+H=rows[hdr[which]]; ci={n:i for i,n in enumerate(H)}   # (each section has its own header: a kernel with local-memory traffic has one more column)
 sec=rows[hdr[which]+1:(hdr[which+1]-1 if which+1<len(hdr) else len(rows))]
 ins=[r for r in sec if len(r)>6 and r[5].isdigit()]
 tot=sum(int(r[5]) for r in ins); tsmp=sum(int(r[2]) for r in ins)
