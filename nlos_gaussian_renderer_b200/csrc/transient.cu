@@ -639,16 +639,17 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         //        kind 0 (both rays wider than 2.5 bins): 1 node, s2 = dt^2/12 (moments to order 3, <= 2.6e-5 of the peak);
                                         //                the two rays of the pair are the two streams of ONE pass
                                         //        kind 1 (wider than 0.8 bins): 2 nodes +-x, x^4 = dt^4/240, s2 = dt^2/12 - x^2 (moments to order 5: the
-                                        //                accuracy of GL3, <= 2.5e-5 of the peak, at the cost of GL2).  Passes: A+-, B+-
-                                        //        kind 2: plain GL4 (s2 = 0).  Passes: A+-, A+-, B+-, B+-.
-                                        //      Without a second ray: A's passes only.
+                                        //                accuracy of GL3, <= 2.5e-5 of the peak, at the cost of GL2).  Passes: {A+, B+}, {A-, B-}
+                                        //        kind 2: plain GL4 (s2 = 0).  Passes: {A+, B+}, {A-, B-} for each of the two node magnitudes.
+                                        //      Without a second ray the two streams of a pass are the mirrored nodes {A+, A-} (half the passes).
                                         const int kind = gpm <= TR_GPM_K0 ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);
                                         const bool two = ok0 && ok1;
                                         const float s2k = kind == 0 ? dt2 * (1.0f / 12.0f) : (kind == 1 ? dt2 * 0.018783611f : 0.f);
                                         float iu0, iu1;
                                         {
                                             // x = C s2 <= 0.03: 1/u and log2(u) by their series (errors < 1e-6)
-                                            const float x0 = R0.gam * (s2k / KG), x1 = R1.gam * (s2k / KG);
+                                            const float s2c = s2k * (1.0f / KG);                              // (a constant multiply, not an IEEE division)
+                                            const float x0 = R0.gam * s2c, x1 = R1.gam * s2c;
                                             iu0 = fmaf(-x0, fmaf(-x0, 1.0f - x0, 1.0f), 1.0f);
                                             iu1 = fmaf(-x1, fmaf(-x1, 1.0f - x1, 1.0f), 1.0f);
                                             R0.al = fmaf(-0.5f * LOG2E_F * x0, fmaf(-x0, fmaf(-x0, 1.0f / 3.0f, 0.5f), 1.0f), R0.al);
@@ -656,35 +657,29 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                             R0.gam *= iu0;
                                             R1.gam *= iu1;
                                         }
-                                        // ray A is the valid one when only one is
+                                        // stream 0 is always ray A (the valid one when only one is).  With two rays stream 1 is ray B and the
+                                        // passes walk the nodes (+x, -x, ..); with one ray stream 1 is ray A at the mirrored node (kind 0: weight 0)
                                         const Ray& RA = ok0 ? R0 : R1;
-                                        const Ray& RB = R1;
-                                        const float wA = (ok0 ? w0 : w1) * dt, wB = w1 * dt;
+                                        const float wA = (ok0 ? w0 : w1) * dt;
+                                        const float gB = two ? R1.gam : RA.gam, aB = two ? R1.al : RA.al, tB = two ? R1.tc : RA.tc;
+                                        const float wB = two ? w1 * dt : (kind == 0 ? 0.f : wA);
                                         const int npass = kind == 0 ? 1 : (two ? 2 * kind : kind);
                                         float SA0 = 0.f, SA1 = 0.f, SA2 = 0.f, SB0 = 0.f, SB1 = 0.f, SB2 = 0.f;
 #pragma unroll 1
                                         for (int ps = 0; ps < npass; ++ps) {
-                                            // pass -> (ray of stream 0, ray of stream 1, node offset, node weight)
-                                            const bool mixed = kind == 0;                                              // stream 0 = ray A, stream 1 = ray B
-                                            const bool onB = two && !mixed && (kind == 2 ? ps >= 2 : ps == 1);
-                                            float xn, wn;
-                                            if (kind == 0) { xn = 0.f; wn = 1.0f; }
-                                            else if (kind == 1) { xn = 0.25406644f; wn = 0.5f; }
-                                            else { xn = (ps & 1) ? 0.43056815579702626f : 0.16999052179242816f; wn = (ps & 1) ? 0.17392742256872692f : 0.32607257743127305f; }
-                                            xn *= dt;
-                                            const float g0 = onB ? RB.gam : RA.gam, a0 = onB ? RB.al : RA.al, t0s = (onB ? RB.tc : RA.tc) + xn;
-                                            const bool s1B = onB || (mixed && two);
-                                            const float g1 = s1B ? RB.gam : RA.gam, a1 = s1B ? RB.al : RA.al, t1s = (s1B ? RB.tc : RA.tc) - xn;
-                                            const float ws0 = (onB ? wB : wA) * wn, ws1 = (mixed && !two) ? 0.f : (s1B ? wB : wA) * wn;
+                                            const int nd = two ? (ps >> 1) : ps;                                     // node of this pass
+                                            float xn = kind == 0 ? 0.f : (kind == 1 ? 0.25406644f : (nd ? 0.43056815579702626f : 0.16999052179242816f));
+                                            const float wn = kind == 0 ? 1.0f : (kind == 1 ? 0.5f : (nd ? 0.17392742256872692f : 0.32607257743127305f));
+                                            xn *= (two && (ps & 1)) ? -dt : dt;
+                                            const float t0s = RA.tc + xn, t1s = two ? tB + xn : tB - xn;
                                             f32x2 E0, G0, E1, G1;
                                             float q0, q1;
-                                            seed(g0, a0, t0s, ws0, E0, G0, q0);
-                                            seed(g1, a1, t1s, ws1, E1, G1, q1);
-                                            float m00 = 0.f, m01 = 0.f, m02 = 0.f, m10 = 0.f, m11 = 0.f, m12 = 0.f;
-                                            run2(E0, G0, q0, E1, G1, q1, nst, t0s, t1s, m00, m01, m02, m10, m11, m12);
+                                            seed(RA.gam, RA.al, t0s, wA * wn, E0, G0, q0);
+                                            seed(gB, aB, t1s, wB * wn, E1, G1, q1);
+                                            float m10 = 0.f, m11 = 0.f, m12 = 0.f;
+                                            run2(E0, G0, q0, E1, G1, q1, nst, t0s, t1s, SA0, SA1, SA2, m10, m11, m12);
                                             if (BWD) {
-                                                if (onB) { SB0 += m00; SB1 += m01; SB2 += m02; } else { SA0 += m00; SA1 += m01; SA2 += m02; }
-                                                if (s1B) { SB0 += m10; SB1 += m11; SB2 += m12; } else { SA0 += m10; SA1 += m11; SA2 += m12; }
+                                                if (two) { SB0 += m10; SB1 += m11; SB2 += m12; } else { SA0 += m10; SA1 += m11; SA2 += m12; }
                                             }
                                         }
                                         if (BWD) {
