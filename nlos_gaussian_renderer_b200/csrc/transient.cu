@@ -379,8 +379,17 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                         f32x2 ACC[FWD ? TR_NH : 1];
                         int nflush = 0;
                         if (FWD) {
+                            // (only the accumulators the pair can touch: steps run to the next multiple of 4 above n_lim at most)
 #pragma unroll
-                            for (int s = 0; s < TR_NH; ++s) ACC[s] = 0ull;
+                            for (int s = 0; s < 8; ++s) ACC[s] = 0ull;
+                            if (n_lim > 8) {
+#pragma unroll
+                                for (int s = 8; s < 16; ++s) ACC[s] = 0ull;
+                                if (n_lim > 16) {
+#pragma unroll
+                                    for (int s = 16; s < TR_NH; ++s) ACC[s] = 0ull;
+                                }
+                            }
                         }
 
                         // ---- ray -> Gaussian in r, re-centred on the sphere through the mean:  a' = a + D b = M (o + D d - mu)
@@ -647,21 +656,25 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         const float s2k = kind == 0 ? dt2 * (1.0f / 12.0f) : (kind == 1 ? dt2 * 0.018783611f : 0.f);
                                         float iu0, iu1;
                                         {
-                                            // x = C s2 <= 0.03: 1/u and log2(u) by their series (errors < 1e-6)
+                                            // x = C s2 <= 0.03: 1/u and log2(u) by their series (errors < 1e-6), both rays at once (packed)
                                             const float s2c = s2k * (1.0f / KG);                              // (a constant multiply, not an IEEE division)
-                                            const float x0 = R0.gam * s2c, x1 = R1.gam * s2c;
-                                            iu0 = fmaf(-x0, fmaf(-x0, 1.0f - x0, 1.0f), 1.0f);
-                                            iu1 = fmaf(-x1, fmaf(-x1, 1.0f - x1, 1.0f), 1.0f);
-                                            R0.al = fmaf(-0.5f * LOG2E_F * x0, fmaf(-x0, fmaf(-x0, 1.0f / 3.0f, 0.5f), 1.0f), R0.al);
-                                            R1.al = fmaf(-0.5f * LOG2E_F * x1, fmaf(-x1, fmaf(-x1, 1.0f / 3.0f, 0.5f), 1.0f), R1.al);
-                                            R0.gam *= iu0;
-                                            R1.gam *= iu1;
+                                            const f32x2 one = pack2(1.0f, 1.0f);
+                                            const f32x2 gm2 = pack2(R0.gam, R1.gam);
+                                            const f32x2 nx = mul2(gm2, pack2(-s2c, -s2c));                                   // -x
+                                            const f32x2 iu = fma2(nx, fma2(nx, add2(one, nx), one), one);                    // 1 - x + x^2 - x^3
+                                            const f32x2 lg = fma2(nx, fma2(nx, pack2(1.0f / 3.0f, 1.0f / 3.0f), pack2(0.5f, 0.5f)), one);   // ln(u) / x
+                                            const f32x2 al2 = fma2(mul2(nx, pack2(0.5f * LOG2E_F, 0.5f * LOG2E_F)), lg, pack2(R0.al, R1.al));
+                                            const f32x2 gi = mul2(gm2, iu);
+                                            unpack2(iu, iu0, iu1);
+                                            unpack2(al2, R0.al, R1.al);
+                                            unpack2(gi, R0.gam, R1.gam);
                                         }
-                                        // stream 0 is always ray A (the valid one when only one is).  With two rays stream 1 is ray B and the
-                                        // passes walk the nodes (+x, -x, ..); with one ray stream 1 is ray A at the mirrored node (kind 0: weight 0)
-                                        const Ray& RA = ok0 ? R0 : R1;
+                                        // stream 0 is ray A, stream 1 ray B: after the copy step above an invalid ray IS its partner (same gam, al, tc),
+                                        // only the weights differ.  With two rays the passes walk the nodes (+x, -x, ..); with one ray stream 1 is the
+                                        // same ray at the mirrored node (kind 0: weight 0)
+                                        const Ray& RA = R0;
                                         const float wA = (ok0 ? w0 : w1) * dt;
-                                        const float gB = two ? R1.gam : RA.gam, aB = two ? R1.al : RA.al, tB = two ? R1.tc : RA.tc;
+                                        const float gB = R1.gam, aB = R1.al, tB = R1.tc;
                                         const float wB = two ? w1 * dt : (kind == 0 ? 0.f : wA);
                                         const int npass = kind == 0 ? 1 : (two ? 2 * kind : kind);
                                         float SA0 = 0.f, SA1 = 0.f, SA2 = 0.f, SB0 = 0.f, SB1 = 0.f, SB2 = 0.f;
@@ -685,7 +698,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         if (BWD) {
                                             // chain rule through the inflation:  d ln e' = -d(m2min)/2 - tau^2 dC / (2 u^2) + C tau dr* / u - s2 dC / (2 u),
                                             // i.e. the moments the plain chain rule expects are  S0, S1 / u, S2 / u^2 + S0 s2 / u
-                                            const float iuA = ok0 ? iu0 : iu1, iuB = iu1;
+                                            const float iuA = iu0, iuB = iu1;                              // (equal when a ray is invalid)
                                             SA2 = fmaf(SA2 * iuA, iuA, SA0 * (s2k * iuA)); SA1 *= iuA;
                                             SB2 = fmaf(SB2 * iuB, iuB, SB0 * (s2k * iuB)); SB1 *= iuB;
                                             // (ray A is R1 when R0 missed the cut: its moments then belong to the second half)
