@@ -228,8 +228,9 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                 __syncwarp();
             }
             auto flush = [&](int cnt) {                       // forward: H[p,k] += acc * hscale_p / (r_k^2 + 1e-8) * flush_scale  (cuda_autograd.py:308-314)
+                const float rcnt = 1.0f / (float)cnt;          // idx / cnt by a multiply: (idx + .5) / cnt stays >= .5 / cnt away from an integer, exact for idx < 2^16
                 for (int idx = lane; idx < cnt * NLOS_TILE; idx += 32) {
-                    const int pp = idx / cnt, kk = idx - pp * cnt, k = base + kk;
+                    const int pp = (int)(((float)idx + 0.5f) * rcnt), kk = idx - pp * cnt, k = base + kk;
                     const float v = Hw[kk * NLOS_TILE + pp];
                     if (v != 0.f && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
@@ -238,8 +239,9 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                 }
             };
             auto refill = [&](int nbase, int kk_from, int cnt) {       // backward: W[k][p] = dL/dH[p,k] * hscale_p / (r_k^2 + 1e-8) * flush_scale
+                const float rcnt = 1.0f / (float)cnt;          // (as in flush)
                 for (int idx = lane; idx < cnt * NLOS_TILE; idx += 32) {
-                    const int pp = idx / cnt, kk = kk_from + (idx - pp * cnt), k = nbase + kk;
+                    const int pp = (int)(((float)idx + 0.5f) * rcnt), kk = kk_from + (idx - pp * cnt), k = nbase + kk;
                     float v = 0.f;
                     if (k >= 0 && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
@@ -530,15 +532,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                 const float* pu = hpc;
                                 const float* pd = hpc - NLOS_TILE;
                                 int s = 0;
-#pragma unroll 1
-                                for (; s < nst; s += 4) {
-                                    if (s >= zmin) {
-                                        float a, b;
-                                        unpack2(E0, a, b); E0 = pack2(s >= zu ? 0.f : a, s >= zd ? 0.f : b);
-                                        unpack2(E1, a, b); E1 = pack2(s >= zu ? 0.f : a, s >= zd ? 0.f : b);
-                                        if (s >= zu) pu = hpc;                      // keep the (ignored) reads inside the window
-                                        if (s >= zd) pd = hpc;
-                                    }
+                                auto block4 = [&]() {
 #pragma unroll
                                     for (int jx = 0; jx < 4; ++jx) {
                                         const f32x2 w2 = pack2(pu[jx * NLOS_TILE], pd[-jx * NLOS_TILE]);
@@ -549,6 +543,20 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         acc_mul2(G0, Q0); acc_mul2(G1, Q1);
                                     }
                                     pu += 4 * NLOS_TILE; pd -= 4 * NLOS_TILE;
+                                };
+                                // phase 1: both directions inside the entry (zmin is a multiple of 4) -- the bare loop
+                                const int n1 = min(nst, zmin);
+#pragma unroll 1
+                                for (; s < n1; s += 4) block4();
+                                // phase 2 (rare): one direction has left the entry and is switched off
+#pragma unroll 1
+                                for (; s < nst; s += 4) {
+                                    float a, b;
+                                    unpack2(E0, a, b); E0 = pack2(s >= zu ? 0.f : a, s >= zd ? 0.f : b);
+                                    unpack2(E1, a, b); E1 = pack2(s >= zu ? 0.f : a, s >= zd ? 0.f : b);
+                                    if (s >= zu) pu = hpc;                          // keep the (ignored) reads inside the window
+                                    if (s >= zd) pd = hpc;
+                                    block4();
                                 }
                                 stream_moments(A0, B0, C0, (float)s, tc0, dt, S0a, S1a, S2a);
                                 stream_moments(A1, B1, C1, (float)s, tc1, dt, S0b, S1b, S2b);
