@@ -304,6 +304,17 @@ def run_b200(args):
                     "mufu_per_sample_eval": mu, "sample_evals_per_s": ws_rank / (ms * 1e-3)}
 
         rb, rf = roof("bwd", bwd_ms), roof("fwd", fwd_ms)
+        traffic = ncu_traffic(args.config, args.mode) if world == 1 else None
+        hbm_view = None
+        try:      # the HBM view of the same launch against the driver-measured copy bandwidth: shows how far from HBM-bound the kernel is
+            hbm_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
+            hbm_src = "MEASURED_PEAKS.json hbm_gbs"
+        except Exception:
+            hbm_peak, hbm_src = 6550.0, "fallback of B200_PROFILING.md (MEASURED_PEAKS.json absent)"
+        if traffic:
+            gbs = traffic / (bwd_ms * 1e-3) / 1e9
+            hbm_view = {"achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "peak_source": hbm_src,
+                        "bytes_per_launch": traffic}
         n_bytes = N * 12 * 4
         line = {
             "metric": "Gaussian-bin evals/s (forward+backward transient)", "value": Wb / (ms_step * 1e-3), "unit": "Gaussian-bin evals/s",
@@ -321,10 +332,10 @@ def run_b200(args):
             "gpu_launches": 9 * args.steps,
             "roofline": {"bound": "compute (" + rb["binding_pipe"] + " pipe)", "kernel": f"transient_kernel<{args.mode},bwd>", "achieved": rb["achieved"],
                          "peak": rb["peak"], "unit": "TFLOP/s", "frac": rb["frac"],
-                         "traffic": ncu_traffic(args.config, args.mode) if world == 1 else None,
+                         "traffic": traffic, "hbm": hbm_view,
                          "peak_source": f"min(148 SM x 128 FP32 lanes x 2 flop, 148 SM x 16 MUFU/clk x flop-per-MUFU of the algorithmic mix) x {f_mhz} MHz "
                                         "(SM clock sampled during the run; SURVEY.md 8d); MEASURED_PEAKS.json holds only HBM and bf16 tensor peaks, "
-                                        "neither binds this kernel (DRAM traffic ~45 MB per launch)",
+                                        "neither binds this kernel (DRAM traffic ~75 MB per launch: see the hbm view)",
                          "sample_evals_per_launch": ws_rank, "bwd": rb, "fwd": rf},
             "loss": float(loss),
         }
