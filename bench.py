@@ -34,6 +34,8 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak (default): every rank renders its own Sy-row slab of a (Sy*N) x Sx grid; strong: the config's grid is split over the ranks")
+    ap.add_argument("--variant", default="auto", choices=["auto", "wide", "narrow"], help="scan-tile kernel per entry (TransientRenderer)")
+    ap.add_argument("--narrow-rays", type=float, default=2.5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-points", type=int, default=0, help="scan points in the CPU baseline sample (0 = auto)")
     return ap.parse_args()
@@ -213,7 +215,7 @@ def run_b200(args):
                         A, vp_y=full.vp_y, device=dev)
     host_params = [p.pin_memory() for p in scenes.make_gaussians(N, seed)]
     params = [p.to(dev) for p in host_params]
-    rnd = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=args.mode)
+    rnd = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=args.mode, variant=args.variant, narrow_rays=args.narrow_rays)
     target = rnd.forward(*[p.to(dev) for p in scenes.make_gaussians(N, seed + 1)]).clone()      # the "measured" transient
     fit = parallel.ShardedFitter(rnd, target, Sy * Sx * T)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -233,15 +235,10 @@ def run_b200(args):
         e[0].record(); Ht = rnd.forward_tiled(); e[1].record()
         loss, gH = rnd.mse_loss_grad_tiled(Ht, fit.target_tiled, 1.0 / fit.numel)      # fused loss + dL/dH (csrc/loss.cu)
         e[2].record()
-        _k = rnd._render_args()
-        from nlos_gaussian_renderer_b200 import _lib
-        _lib.call("nlosb200_transient_backward", *_k, rnd.c_deltaT, rnd.mcut, rnd.mode, gH.data_ptr(), rnd.dacc.data_ptr(), _lib.stream())
+        rnd.render_backward(gH)
         e[3].record()
         parallel.all_reduce_packed(rnd.dacc)
-        means, ls, rots, opac, feats = rnd._params
-        outs = [torch.empty_like(means), torch.empty_like(ls), torch.empty_like(rots), torch.empty_like(opac), torch.empty_like(feats)]
-        _lib.call("nlosb200_preprocess_backward", ls.data_ptr(), rots.data_ptr(), opac.data_ptr(), feats.data_ptr(), N, feats.shape[1],
-                  rnd.mod, rnd.dacc.data_ptr(), *[o.data_ptr() for o in outs], 0, _lib.stream())
+        outs = rnd.chain()
         if record:
             kt["fwd"].append((e[0], e[1]))
             kt["bwd"].append((e[2], e[3]))

@@ -54,32 +54,47 @@ int nlosb200_build_scan_tiles(const float* scan_o, const float* sin_th, const fl
  * accumulator is a sliding window of `window` bins (multiple of 8) advancing in steps of `bucket` bins, so a Gaussian is
  * listed once per tile unless its interval is longer than L = window-bucket (then entry e covers [klo+eL, klo+(e+1)L-1]).
  * Entry (g,e) lives in cell (tile, (klo+eL)/bucket); list value = g | e<<26; per cell ascending g.
- * n_buckets = ceil(T/bucket) <= 64, n_cells = n_tiles*n_buckets.
+ * n_buckets = ceil(T/bucket) <= 64.  Entry classes: with n_classes = 2 the cells of a tile are class-major (n_cells = n_tiles * n_classes *
+ * n_buckets, cell = tile * 2 n_buckets + cls * n_buckets + bucket); an entry is class 0 ("narrow") when its Gaussian is listed once in the tile
+ * and (6 / mcut) rad <= narrow_rays * pitch * min-distance, pitch = the smallest lattice step of the tile's scan points -- i.e. its 3-sigma AABB
+ * spans at most narrow_rays lattice pitches -- else class 1.  n_classes = 1 (narrow_rays = 0): a single class.
  * chunk_counts int32 [n_cells * nlosb200_bin_num_chunks(N)], cell_counts int32 [n_cells], cell_offsets int64 [n_cells+1],
  * tile_items int32 [n_tiles+1], header int64 [4] = {total list entries, CTA work items, overflow flag, -}. */
 int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                             int window, int bucket, int slice_len, int warps_per_block, int* chunk_counts, int* cell_counts,
-                             long long* cell_offsets, int* tile_items, long long* header, void* stream);
+                             int window, int bucket, int n_classes, float narrow_rays, float mcut, int slice_len, int warps_per_block,
+                             int* chunk_counts, int* cell_counts, long long* cell_offsets, int* tile_items, long long* header, void* stream);
 int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                             int window, int bucket, const int* chunk_counts_scanned, const long long* cell_offsets, int* list,
-                             int* list_bins, long long list_capacity, long long* header, void* stream);
+                             int window, int bucket, int n_classes, float narrow_rays, float mcut, const int* chunk_counts_scanned,
+                             const long long* cell_offsets, int* list, int* list_bins, long long list_capacity, long long* header,
+                             void* stream);
 
 /* ---- batched transient H[n_tiles*32, T] and its backward.  mode 0 = numerical (volume_renderer.cu
  * no-occlusion branch :139-182), 1 = analytic-exact per-bin integral.
- * bin k sits at radius t0 + k*dt.  H and dacc are zeroed by the callee.  list_bins[i] = klo | khi << 16 is the tile-level shell of
- * entry i as written by nlosb200_bin_window_fill (T <= 65535).  `work` is int32 scratch [n_tiles] (zeroed by the callee):
- * the per-tile slice counters the persistent CTAs pull work from; slice_len = list entries a warp takes at a time. */
+ * bin k sits at radius t0 + k*dt.  list_bins[i] = klo | khi << 16 is the tile-level shell of entry i as written by
+ * nlosb200_bin_window_fill (T <= 65535); list_capacity = entries the two list buffers hold (a launch whose lists do not fit renders
+ * nothing: the overflow flag of bin_window_fill tells).  The cells of a tile are class-major: n_classes * n_buckets per tile, a launch
+ * walks class `cls` (nlosb200_bin_window_plan).  variant 0 = register-accumulator kernel (wide footprints, transient.cu), 1 = direct-to-window
+ * kernel (footprints of a few rays, transient_narrow.cu); both render any entry, they differ in speed only.  accumulate = 0: H / dacc /
+ * counters are zeroed by the callee first; 1: the launch adds to them (second class).  `work` is int32 scratch [n_tiles] (zeroed by the
+ * callee): the per-tile slice counters the persistent CTAs pull work from; slice_len = list entries a warp takes at a time. */
 int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                               const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
-                               int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, float* H, void* stream);
+                               const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
+                               int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
+                               int mode, int variant, int accumulate, float* H, void* stream);
 int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
-                                int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, const float* grad_H,
-                                float* dacc, void* stream);
+                                const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
+                                int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
+                                int mode, int variant, int accumulate, const float* grad_H, float* dacc, void* stream);
 /* counters uint64 [4]: hit (g,ray) pairs, W_s, sample-evals evaluated, W_b */
 int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                             const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
-                             int window, int bucket, int slice_len, float mcut, unsigned long long* counters, void* stream);
+                             const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
+                             int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float mcut, int accumulate,
+                             unsigned long long* counters, void* stream);
+
+/* tests only: while `hits` is non-NULL every render launch also marks the (scan point, ray, Gaussian) triples that pass its slab test in the
+ * dense byte array hits [n_tiles*32][A*A][N] (caller zeroes) -- compared bit for bit with the reference's per-ray filter lists
+ * (src/ray_aabb.cu:10-61).  Pass NULL to switch the dump off. */
+int nlosb200_debug_hit_dump(unsigned char* hits);
 
 /* ==== one-scan-point operators: the reference's pybind module nlos_gaussian_renderer._C ===========================
  * (submodules/cuda_renderer/src/bindings.cpp:26-35).  A Python/torch caller allocates the outputs and passes

@@ -12,6 +12,12 @@
 // is g | e << 26.  Definition and bit-exact operation order: oracle/nlos_oracle.c:orc_shell_bins and
 // oracle/__init__.py:window_lists.
 //
+// Entry classes (n_classes = 2): the cells of a tile are class-major, cell = tile * 2 n_buckets + cls * n_buckets + bucket.  An entry is
+// class 0 ("narrow": rendered by transient_narrow.cu) when the Gaussian is listed once in the tile (interval <= L) and its 3-sigma AABB
+// spans at most `narrow_rays` lattice pitches of the tile:  (6 / mcut) rad <= narrow_rays * pitch * sqrt(min_p |mu - o_p|^2) , with
+// rad = mcut max(scale) from the shell and pitch = the smallest angular step (dtheta, dphi) of the tile's scan points; otherwise class 1.
+// Same single-rounding operation order in oracle/__init__.py:entry_classes.
+//
 // Passes (all stream ordered, no host sync inside):
 //   count : per (tile, chunk of 1024 Gaussians) histogram of cell membership
 //   scan  : per cell exclusive scan over chunks; then over cells (int64 offsets), and the render work
@@ -29,6 +35,7 @@ using namespace nlos;
 
 struct TilePoints {
     float ox[NLOS_TILE], oy[NLOS_TILE], oz[NLOS_TILE];
+    float step[NLOS_TILE];     // min(dtheta, dphi) of the scan point's lattice (0: no usable lattice)
     int valid[NLOS_TILE];
 };
 
@@ -42,13 +49,16 @@ __device__ __forceinline__ void load_tile_points(TilePoints& tp, const float* __
         tp.oy[l] = pi[PI_OY * NLOS_TILE + l];
         tp.oz[l] = pi[PI_OZ * NLOS_TILE + l];
         tp.valid[l] = __float_as_int(pi[PI_FLAGS * NLOS_TILE + l]) & 1;
+        tp.step[l] = (__float_as_int(pi[PI_FLAGS * NLOS_TILE + l]) & 2) ? fminf(pi[PI_DTH * NLOS_TILE + l], pi[PI_DPH * NLOS_TILE + l]) : 0.f;
     }
 }
 
 // oracle/nlos_oracle.c:orc_shell_bins, same single-rounding operation order.  klo > khi = empty.
-__device__ __forceinline__ void shell_bins(const TilePoints& tp, float4 sh, float t0, float inv_dt, int T, int& klo, int& khi)
+// cls: 0 = narrow entry, 1 = wide (header comment); narrow_k = narrow_rays (0: a single class, everything is class 0), rad_k = 6 / mcut.
+__device__ __forceinline__ void shell_bins(const TilePoints& tp, float4 sh, float t0, float inv_dt, int T, int L, float narrow_k, float rad_k,
+                                           int& klo, int& khi, int& cls)
 {
-    float d2min = INFINITY, d2max = 0.0f;
+    float d2min = INFINITY, d2max = 0.0f, pitch = INFINITY;
 #pragma unroll 8
     for (int l = 0; l < NLOS_TILE; ++l) {
         if (!tp.valid[l]) continue;
@@ -56,12 +66,18 @@ __device__ __forceinline__ void shell_bins(const TilePoints& tp, float4 sh, floa
         float d2 = __fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz));
         d2min = fminf(d2min, d2);
         d2max = fmaxf(d2max, d2);
+        pitch = fminf(pitch, tp.step[l]);
     }
     float rlo = __fsub_rn(__fsqrt_rn(d2min), sh.w), rhi = __fadd_rn(__fsqrt_rn(d2max), sh.w);
     float klo_f = floorf(__fadd_rn(__fmul_rn(__fsub_rn(rlo, t0), inv_dt), 0.5f));
     float khi_f = floorf(__fadd_rn(__fmul_rn(__fsub_rn(rhi, t0), inv_dt), 0.5f));
     klo = klo_f < 0.0f ? 0 : (klo_f > (float)(T - 1) ? T : (int)klo_f);
     khi = khi_f < 0.0f ? -1 : (khi_f > (float)(T - 1) ? T - 1 : (int)khi_f);
+    cls = 0;
+    if (narrow_k > 0.f) {
+        bool narrow = khi - klo + 1 <= L && __fmul_rn(sh.w, rad_k) <= __fmul_rn(__fmul_rn(narrow_k, pitch), __fsqrt_rn(d2min));
+        cls = narrow ? 0 : 1;
+    }
 }
 
 // sub-interval index e of the entry of [klo, khi] that lives in bucket r, or -1  (L > bucket => at most one)
@@ -77,25 +93,26 @@ __device__ __forceinline__ int entry_in_bucket(int klo, int khi, int r, int L, i
 
 __global__ void __launch_bounds__(BIN_THREADS) shell_count_kernel(const float* __restrict__ tiles, int A, const float4* __restrict__ shell, int N,
                                                                   float t0, float inv_dt, int T, int L, int bucket, int n_buckets, int n_chunks,
-                                                                  int* __restrict__ chunk_counts)
+                                                                  int n_classes, float narrow_k, float rad_k, int* __restrict__ chunk_counts)
 {
     __shared__ TilePoints tp;
-    __shared__ int cnt[BIN_MAX_RANGES];
+    __shared__ int cnt[2 * BIN_MAX_RANGES];
     int tile = blockIdx.y, chunk = blockIdx.x;
     load_tile_points(tp, tiles, tile, A);
-    if (threadIdx.x < BIN_MAX_RANGES) cnt[threadIdx.x] = 0;
+    if (threadIdx.x < 2 * BIN_MAX_RANGES) cnt[threadIdx.x] = 0;
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < BIN_GPT; ++j) {
         int g = chunk * BIN_CHUNK + j * BIN_THREADS + threadIdx.x;
         if (g < N) {
-            int klo, khi;
-            shell_bins(tp, shell[g], t0, inv_dt, T, klo, khi);
-            for (int s = klo; s <= khi; s += L) atomicAdd(&cnt[s / bucket], 1);
+            int klo, khi, cls;
+            shell_bins(tp, shell[g], t0, inv_dt, T, L, narrow_k, rad_k, klo, khi, cls);
+            for (int s = klo; s <= khi; s += L) atomicAdd(&cnt[cls * n_buckets + s / bucket], 1);
         }
     }
     __syncthreads();
-    if (threadIdx.x < n_buckets) chunk_counts[((size_t)tile * n_buckets + threadIdx.x) * n_chunks + chunk] = cnt[threadIdx.x];
+    const int cpt = n_classes * n_buckets;
+    if (threadIdx.x < cpt) chunk_counts[((size_t)tile * cpt + threadIdx.x) * n_chunks + chunk] = cnt[threadIdx.x];
 }
 
 // per cell: exclusive scan over chunks (in place) and the cell total
@@ -122,7 +139,7 @@ __global__ void __launch_bounds__(256) scan_chunks_kernel(int* __restrict__ chun
 
 // single CTA: cell offsets (int64), CTA-item prefix per tile, header
 //   header[0] = total list entries, header[1] = number of CTA work items, header[2] = overflow flag (set by fill)
-__global__ void __launch_bounds__(1024) scan_cells_kernel(const int* __restrict__ cell_counts, int n_tiles, int n_buckets, int slice_len, int wpb,
+__global__ void __launch_bounds__(1024) scan_cells_kernel(const int* __restrict__ cell_counts, int n_tiles, int n_buckets /* cells per tile */, int slice_len, int wpb,
                                                           long long* __restrict__ cell_offsets, int* __restrict__ tile_items,
                                                           long long* __restrict__ header)
 {
@@ -175,32 +192,36 @@ __global__ void __launch_bounds__(1024) scan_cells_kernel(const int* __restrict_
 
 __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __restrict__ tiles, int A, const float4* __restrict__ shell, int N,
                                                                  float t0, float inv_dt, int T, int L, int bucket, int n_buckets, int n_chunks,
+                                                                 int n_classes, float narrow_k, float rad_k,
                                                                  const int* __restrict__ chunk_off, const long long* __restrict__ cell_offsets,
                                                                  unsigned* __restrict__ list, unsigned* __restrict__ list_bins, long long capacity,
                                                                  long long* __restrict__ header)
 {
     __shared__ TilePoints tp;
-    __shared__ int wc[BIN_GPT][BIN_THREADS / 32][BIN_MAX_RANGES];
+    __shared__ int wc[BIN_GPT][BIN_THREADS / 32][2 * BIN_MAX_RANGES];
     int tile = blockIdx.y, chunk = blockIdx.x;
+    const int cpt = n_classes * n_buckets;
     int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     load_tile_points(tp, tiles, tile, A);
     __syncthreads();
-    int lo[BIN_GPT], hi[BIN_GPT];
+    int lo[BIN_GPT], hi[BIN_GPT], cl[BIN_GPT];
 #pragma unroll
     for (int j = 0; j < BIN_GPT; ++j) {
         int g = chunk * BIN_CHUNK + j * BIN_THREADS + threadIdx.x;
         lo[j] = 1;
         hi[j] = 0;
-        if (g < N) shell_bins(tp, shell[g], t0, inv_dt, T, lo[j], hi[j]);
+        cl[j] = 0;
+        if (g < N) shell_bins(tp, shell[g], t0, inv_dt, T, L, narrow_k, rad_k, lo[j], hi[j], cl[j]);
     }
 #pragma unroll
     for (int j = 0; j < BIN_GPT; ++j)
-        for (int r = 0; r < n_buckets; ++r) {
-            unsigned b = __ballot_sync(0xffffffffu, entry_in_bucket(lo[j], hi[j], r, L, bucket) >= 0);
-            if (lane == 0) wc[j][warp][r] = __popc(b);
+        for (int c = 0; c < cpt; ++c) {
+            const int r = c < n_buckets ? c : c - n_buckets, k = c < n_buckets ? 0 : 1;
+            unsigned b = __ballot_sync(0xffffffffu, cl[j] == k && entry_in_bucket(lo[j], hi[j], r, L, bucket) >= 0);
+            if (lane == 0) wc[j][warp][c] = __popc(b);
         }
     __syncthreads();
-    if (threadIdx.x < n_buckets) {
+    if (threadIdx.x < cpt) {
         int r = threadIdx.x, run = 0;
         for (int j = 0; j < BIN_GPT; ++j)
             for (int w = 0; w < BIN_THREADS / 32; ++w) { int v = wc[j][w][r]; wc[j][w][r] = run; run += v; }
@@ -210,12 +231,13 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __
 #pragma unroll
     for (int j = 0; j < BIN_GPT; ++j) {
         int g = chunk * BIN_CHUNK + j * BIN_THREADS + threadIdx.x;
-        for (int r = 0; r < n_buckets; ++r) {
-            int e = entry_in_bucket(lo[j], hi[j], r, L, bucket);
+        for (int c = 0; c < cpt; ++c) {
+            const int r = c < n_buckets ? c : c - n_buckets, k = c < n_buckets ? 0 : 1;
+            int e = cl[j] == k ? entry_in_bucket(lo[j], hi[j], r, L, bucket) : -1;
             unsigned b = __ballot_sync(0xffffffffu, e >= 0);
             if (e >= 0) {
-                size_t cell = (size_t)tile * n_buckets + r;
-                long long pos = cell_offsets[cell] + chunk_off[cell * n_chunks + chunk] + wc[j][warp][r] + __popc(b & lt);
+                size_t cell = (size_t)tile * cpt + c;
+                long long pos = cell_offsets[cell] + chunk_off[cell * n_chunks + chunk] + wc[j][warp][c] + __popc(b & lt);
                 if (pos < capacity) {
                     list[pos] = (unsigned)g | ((unsigned)e << NLOS_ENTRY_SHIFT);
                     if (list_bins) list_bins[pos] = (unsigned)lo[j] | ((unsigned)hi[j] << 16);      // the Gaussian's tile-level shell [klo, khi]
@@ -239,13 +261,25 @@ static int check_window(const char* who, int T, int window, int bucket, int N)
     return 0;
 }
 
+static int check_classes(const char* who, int n_classes, float narrow_rays, float mcut)
+{
+    NLOS_REQUIRE(n_classes == 1 || n_classes == 2, "%s: n_classes=%d must be 1 or 2", who, n_classes);
+    NLOS_REQUIRE(n_classes == 1 ? narrow_rays == 0.f : narrow_rays > 0.f, "%s: narrow_rays must be > 0 with two classes and 0 with one", who);
+    NLOS_REQUIRE(n_classes == 1 || mcut > 0.f, "%s: mcut must be > 0", who);
+    return 0;
+}
+
 extern "C" int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                                        int window, int bucket, int slice_len, int warps_per_block, int* chunk_counts, int* cell_counts,
-                                        long long* cell_offsets, int* tile_items, long long* header, void* stream)
+                                        int window, int bucket, int n_classes, float narrow_rays, float mcut, int slice_len, int warps_per_block,
+                                        int* chunk_counts, int* cell_counts, long long* cell_offsets, int* tile_items, long long* header,
+                                        void* stream)
 {
     NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && slice_len > 0 && warps_per_block > 0, "bin_window_plan: bad sizes");
     int rc = check_window("bin_window_plan", T, window, bucket, N);
     if (rc) return rc;
+    rc = check_classes("bin_window_plan", n_classes, narrow_rays, mcut);
+    if (rc) return rc;
+    const float rad_k = n_classes == 2 ? 6.0f / mcut : 0.f;
     int n_buckets = (T + bucket - 1) / bucket;
     NLOS_REQUIRE(n_tiles <= 65535, "bin_window_plan: n_tiles=%d > 65535 (shard the scan grid)", n_tiles);
     NLOS_REQUIRE(tiles && shell && chunk_counts && cell_counts && cell_offsets && tile_items && header, "bin_window_plan: null pointer");
@@ -253,30 +287,35 @@ extern "C" int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, 
     float inv_dt = 1.0f / dt;
     cudaStream_t s = (cudaStream_t)stream;
     shell_count_kernel<<<dim3(n_chunks, n_tiles), BIN_THREADS, 0, s>>>(tiles, A, reinterpret_cast<const float4*>(shell), N, t0, inv_dt, T,
-                                                                       window - bucket, bucket, n_buckets, n_chunks, chunk_counts);
+                                                                       window - bucket, bucket, n_buckets, n_chunks, n_classes, narrow_rays, rad_k,
+                                                                       chunk_counts);
     NLOS_CHECK_LAUNCH("shell_count_kernel");
-    scan_chunks_kernel<<<n_tiles * n_buckets, 256, 0, s>>>(chunk_counts, n_chunks, cell_counts);
+    scan_chunks_kernel<<<n_tiles * n_buckets * n_classes, 256, 0, s>>>(chunk_counts, n_chunks, cell_counts);
     NLOS_CHECK_LAUNCH("scan_chunks_kernel");
-    scan_cells_kernel<<<1, 1024, 0, s>>>(cell_counts, n_tiles, n_buckets, slice_len, warps_per_block, cell_offsets, tile_items, header);
+    scan_cells_kernel<<<1, 1024, 0, s>>>(cell_counts, n_tiles, n_buckets * n_classes, slice_len, warps_per_block, cell_offsets, tile_items, header);
     NLOS_CHECK_LAUNCH("scan_cells_kernel");
     return 0;
 }
 
 extern "C" int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                                        int window, int bucket, const int* chunk_counts_scanned, const long long* cell_offsets, int* list,
-                                        int* list_bins, long long list_capacity, long long* header, void* stream)
+                                        int window, int bucket, int n_classes, float narrow_rays, float mcut, const int* chunk_counts_scanned,
+                                        const long long* cell_offsets, int* list, int* list_bins, long long list_capacity, long long* header,
+                                        void* stream)
 {
     NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0, "bin_window_fill: bad sizes");
     int rc = check_window("bin_window_fill", T, window, bucket, N);
     if (rc) return rc;
+    rc = check_classes("bin_window_fill", n_classes, narrow_rays, mcut);
+    if (rc) return rc;
+    const float rad_k = n_classes == 2 ? 6.0f / mcut : 0.f;
     int n_buckets = (T + bucket - 1) / bucket;
     NLOS_REQUIRE(list || list_capacity == 0, "bin_window_fill: null list");
     NLOS_REQUIRE(!list_bins || T <= 65535, "bin_window_fill: list_bins packs two 16-bit bins (T=%d)", T);
     int n_chunks = (N + BIN_CHUNK - 1) / BIN_CHUNK;
     float inv_dt = 1.0f / dt;
     shell_fill_kernel<<<dim3(n_chunks, n_tiles), BIN_THREADS, 0, (cudaStream_t)stream>>>(
-        tiles, A, reinterpret_cast<const float4*>(shell), N, t0, inv_dt, T, window - bucket, bucket, n_buckets, n_chunks, chunk_counts_scanned,
-        cell_offsets, reinterpret_cast<unsigned*>(list), reinterpret_cast<unsigned*>(list_bins), list_capacity, header);
+        tiles, A, reinterpret_cast<const float4*>(shell), N, t0, inv_dt, T, window - bucket, bucket, n_buckets, n_chunks, n_classes, narrow_rays,
+        rad_k, chunk_counts_scanned, cell_offsets, reinterpret_cast<unsigned*>(list), reinterpret_cast<unsigned*>(list_bins), list_capacity, header);
     NLOS_CHECK_LAUNCH("shell_fill_kernel");
     return 0;
 }

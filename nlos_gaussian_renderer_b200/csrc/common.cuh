@@ -27,6 +27,7 @@
 #define REC_ALB 19    // degree-0 albedo  max(C0*f0 + 0.5, 0)
 #define REC_RAD 20    // mcut * max(scale)
 #define REC_S 21      // 21..23 activated scales
+#define REC_EXT 24    // 24..26 half extents of the 3-sigma AABB about the mean (rounded up), 27 their norm Rb
 
 // lattice tables per tile (NLOS_NTAB * A rows of 32 lanes):
 //   theta block  [A][3][32] : row i -> sin(theta_i), cos(theta_i), tan(theta_i)
@@ -51,6 +52,9 @@
 #define PI_IDPH 6
 #define PI_HSCALE 7
 #define PI_FLAGS 8    // bit0 valid, bit1 fast footprint ok
+#define PI_DTH 10     // lattice steps (the linspace's, theta / phi)
+#define PI_DPH 11
+#define PI_ISTMAX 9   // max_i 1 / sin(theta_i) of the scan point's lattice (bound used by the borderline band of the slab test)
 
 #define NLOS_SH_C0 0.28209479177387814f
 

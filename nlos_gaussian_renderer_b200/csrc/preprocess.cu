@@ -69,7 +69,10 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const float* __restrict
     rec[3] = make_float4(R[8] * is2, bmin[0], bmin[1], bmin[2]);
     rec[4] = make_float4(bmax[0], bmax[1], bmax[2], alb);
     rec[5] = make_float4(rad, sx, sy, sz);
-    rec[6] = make_float4(0.f, 0.f, 0.f, 0.f);
+    // half extents of the AABB about the mean as the render kernels see them (max distance of a box face from mu, rounded up) and their norm
+    float hx = fmaxf(mx - bmin[0], bmax[0] - mx) * 1.00001f + 1e-9f, hy = fmaxf(my - bmin[1], bmax[1] - my) * 1.00001f + 1e-9f,
+          hz = fmaxf(mz - bmin[2], bmax[2] - mz) * 1.00001f + 1e-9f;
+    rec[6] = make_float4(hx, hy, hz, sqrtf(hx * hx + hy * hy + hz * hz) * 1.00001f);
     rec[7] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
@@ -207,8 +210,10 @@ __global__ void __launch_bounds__(128) build_scan_tiles_kernel(const float* __re
     float* tb = tiles + tile * tile_floats;
     float* pi = tb + (size_t)NLOS_NTAB * A * NLOS_TILE;
     bool valid = p < S && (!valid_mask || valid_mask[p] != 0);
+    float istmax = 1.f;
     for (int i = 0; i < A; ++i) {
         float st = valid ? sin_th[(size_t)p * A + i] : 1.f, ct = valid ? cos_th[(size_t)p * A + i] : 1.f;
+        istmax = fmaxf(istmax, 1.0f / fmaxf(fabsf(st), 1e-12f));
         float sp = valid ? sin_ph[(size_t)p * A + i] : 1.f, cp = valid ? cos_ph[(size_t)p * A + i] : 1.f;
         tb[TAB_TH(A, i) + TH_SIN + lane] = st;
         tb[TAB_TH(A, i) + TH_COS + lane] = ct;
@@ -232,7 +237,9 @@ __global__ void __launch_bounds__(128) build_scan_tiles_kernel(const float* __re
     pi[PI_IDPH * NLOS_TILE + lane] = fast ? 1.0f / dph : 0.f;
     pi[PI_HSCALE * NLOS_TILE + lane] = valid ? hscale[p] : 0.f;
     pi[PI_FLAGS * NLOS_TILE + lane] = __int_as_float((valid ? 1 : 0) | (fast ? 2 : 0));
-    for (int r = PI_FLAGS + 1; r < NLOS_PINFO_ROWS; ++r) pi[r * NLOS_TILE + lane] = 0.f;
+    pi[PI_ISTMAX * NLOS_TILE + lane] = istmax;
+    pi[PI_DTH * NLOS_TILE + lane] = dth;
+    pi[PI_DPH * NLOS_TILE + lane] = dph;
 }
 
 extern "C" int nlosb200_build_scan_tiles(const float* scan_o, const float* sin_th, const float* cos_th, const float* sin_ph,

@@ -32,97 +32,7 @@
 //      Gaussians (rays wider than 2.5 / 0.8 bins; <= 2.6e-5 of the peak per ray, below the 1e-4 parity tolerance) or with
 //      GL4 nodes: each node is one more recurrence stream on the same registers.  Rays narrower than 0.6 bins, or whose
 //      seeds are not representable, take the closed-form erf path (analytic) / the direct 1-MUFU-per-bin path (numerical).
-#include "common.cuh"
-#include "../../include/nlosb200.h"
-
-using namespace nlos;
-
-#ifndef TR_WPB
-#define TR_WPB 12          // warps per CTA
-#endif
-#define TR_MINB 1          // CTAs per SM the register allocation is sized for
-#define TR_RING 4          // records per ring stage
-#define TR_STAGES 2
-#define TR_NH 32           // forward: register accumulators cover bins [kc - TR_NH, kc + TR_NH)
-#define TR_GUARD 4         // zero bins on either side of a warp's window (backward reads up to 3 bins past an entry)
-#define LOG2E_F 1.4426950408889634f
-#define SQRT_PI_2 1.2533141373155001f
-#define NO_BASE (-0x40000000)
-// analytic mode: gpm = 0.72 / (ray width in bins)^2 up to which the 1-node / 2-node moment-matched mixtures are used
-#ifndef TR_GPM_K0
-#define TR_GPM_K0 0.115f   // >= 2.5 bins
-#endif
-#ifndef TR_GPM_K1
-#define TR_GPM_K1 1.125f   // >= 0.8 bins
-#endif
-
-enum { MODE_NUM = 0, MODE_ANA = 1, MODE_COUNT = 2 };
-
-struct TransientParams {
-    const float* tiles;
-    int n_tiles, A;
-    const float* records;
-    int N;
-    const unsigned* list;            // entries g | e << NLOS_ENTRY_SHIFT, tile-major, ordered by bucket
-    const unsigned* list_bins;       // per entry: tile-level shell klo | khi << 16 (binning.cu:shell_fill_kernel)
-    const long long* cell_offsets;   // [n_tiles*n_buckets + 1]
-    int* work;                       // [n_tiles] next slice of every tile's entry list (zeroed before the launch)
-    float t0, dt, inv_dt;
-    int T, window, bucket, n_buckets, slice_len;
-    float flush_scale;   // c*deltaT for the numerical mode (volume_renderer.cu:182), 1 for the analytic-exact mode
-    float mcut2;
-    float* H;            // forward out   [n_tiles*32, T]  (accumulated with REDs; caller zeroes)
-    const float* gH;     // backward in   [n_tiles*32, T]
-    float* dacc;         // backward out  [N, 16]          (accumulated with REDs; caller zeroes)
-    unsigned long long* counters;   // MODE_COUNT: [0] hit (g,ray) pairs, [1] W_s, [2] evaluated sample-evals, [3] W_b
-};
-
-__device__ __forceinline__ int clamp_ceil(float x, int lo, int hi)
-{
-    x = ceilf(x);
-    return x <= (float)lo ? lo : (x >= (float)hi ? hi : (int)x);
-}
-__device__ __forceinline__ int clamp_floor(float x, int lo, int hi)
-{
-    x = floorf(x);
-    return x <= (float)lo ? lo : (x >= (float)hi ? hi : (int)x);
-}
-// 1/x to ~1 ulp: MUFU.RCP + one Newton step instead of the ~10-instruction IEEE division
-__device__ __forceinline__ float rcp_nr(float x)
-{
-    float r = rcp_approx(x);
-    return r * fmaf(-x, r, 2.0f);
-}
-__device__ __forceinline__ float rsqrt_approx(float x)
-{
-    float y;
-    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-    return y;
-}
-__device__ __forceinline__ float lo_of(f32x2 v) { float a, b; unpack2(v, a, b); return a; }
-__device__ __forceinline__ float hi_of(f32x2 v) { float a, b; unpack2(v, a, b); return b; }
-
-// moments of one packed {up, down} stream after n executed steps:  x_s = w e at step s,
-//   A = sum x,  B = sum_s A_s = sum x (n - s),  C = sum_s B_s = sum x (n-s)(n-s+1)/2
-// up bin kc+s has tau = tc + s dt, down bin kc-1-s has tau = tc - dt - s dt.
-__device__ __forceinline__ void stream_moments(f32x2 A, f32x2 B, f32x2 C, float nf, float tc, float dt, float& S0, float& S1, float& S2)
-{
-    // evaluated on the packed {up, down} halves, then the two halves are added
-    const f32x2 n2 = pack2(nf, nf), neg1 = pack2(-1.0f, -1.0f), two = pack2(2.0f, 2.0f);
-    const f32x2 nB = mul2(B, neg1);
-    const f32x2 M1 = fma2(n2, A, nB);                                                       // sum x s
-    const f32x2 M2 = fma2(n2, fma2(n2, A, add2(nB, nB)), fma2(two, C, nB));                 // sum x s^2
-    const float td = tc - dt, dt2 = dt * dt;
-    const f32x2 T1 = pack2(tc, td), DT = pack2(dt, -dt);
-    const f32x2 T2 = mul2(T1, T1), TT = mul2(mul2(T1, DT), two);
-    const f32x2 s1 = fma2(T1, A, mul2(DT, M1));
-    const f32x2 s2 = fma2(T2, A, fma2(TT, M1, mul2(pack2(dt2, dt2), M2)));
-    float a0, a1, b0, b1, c0, c1;
-    unpack2(A, a0, a1); unpack2(s1, b0, b1); unpack2(s2, c0, c1);
-    S0 += a0 + a1;
-    S1 += b0 + b1;
-    S2 += c0 + c1;
-}
+#include "transient_shared.cuh"
 
 template <int MODE, bool BWD>
 __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const TransientParams P)
@@ -142,6 +52,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_ring + TR_WPB * TR_STAGES * TR_RING * NLOS_REC_FLOATS);   // [1 + TR_WPB*TR_STAGES]
     int* s_ctl = reinterpret_cast<int*>(s_bar + 1 + TR_WPB * TR_STAGES);                                      // [2] next tile, tiles consumed
 
+    if (P.cell_offsets[(size_t)P.n_tiles * P.cpt] > P.list_capacity) return;   // list buffer overflow (flagged by bin_window_fill): render nothing
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         mbar_init(&s_bar[0], 1);
@@ -174,7 +85,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                 if (visited + off < P.n_tiles) {
                     int t = t_cur + off;
                     if (t >= P.n_tiles) t -= P.n_tiles;
-                    const long long tot = P.cell_offsets[(size_t)(t + 1) * P.n_buckets] - P.cell_offsets[(size_t)t * P.n_buckets];
+                    const long long tot = P.cell_offsets[(size_t)t * P.cpt + P.cell0 + P.n_buckets] - P.cell_offsets[(size_t)t * P.cpt + P.cell0];
                     has = *(volatile int*)(P.work + t) < (int)((tot + P.slice_len - 1) / P.slice_len);
                 }
                 const unsigned m = __ballot_sync(0xffffffffu, has);
@@ -200,8 +111,8 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
             mbar_arrive_expect_tx(&s_bar[0], (uint32_t)tile_floats * 4u);
             bulk_g2s(s_tab, P.tiles + (size_t)tile * tile_floats, (uint32_t)tile_floats * 4u, &s_bar[0]);
         }
-        const long long tile_beg = P.cell_offsets[(size_t)tile * P.n_buckets];
-        const long long tile_tot = P.cell_offsets[(size_t)(tile + 1) * P.n_buckets] - tile_beg;
+        const long long tile_beg = P.cell_offsets[(size_t)tile * P.cpt + P.cell0];
+        const long long tile_tot = P.cell_offsets[(size_t)tile * P.cpt + P.cell0 + P.n_buckets] - tile_beg;
         const int n_slices = (int)((tile_tot + P.slice_len - 1) / P.slice_len);
         mbar_wait(&s_bar[0], tphase);   // lattice tables + scan-point info have landed
         tphase ^= 1u;
@@ -210,6 +121,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
         const float ox = s_pi[PI_OX * 32 + lane], oy = s_pi[PI_OY * 32 + lane], oz = s_pi[PI_OZ * 32 + lane];
         const int flags = __float_as_int(s_pi[PI_FLAGS * 32 + lane]);
         const bool valid = flags & 1, fast = flags & 2;
+        const float kband = 1.5e-8f * s_pi[PI_ISTMAX * 32 + lane];      // borderline band of the slab test per unit of 1/|d_axis|
 
         for (;;) {
             int sl = 0;
@@ -568,16 +480,21 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                             for (int jb = j0; jb <= j1; jb += 8) {
                                 const float* const thb = tabl + TAB_TH(A, ib);
                                 const float* const phb = tabl + TAB_PH(A, jb);
-                                // ---- 1. exact slab test of every candidate ray of this 4x8 block -> hit mask (bit = 8*row + column).
+                                // ---- 1. slab test of every candidate ray of this 4x8 block -> hit mask (bit = 8*row + column).
                                 //         cuda_utils.cuh:97-121 with every t multiplied by sin(theta) > 0: the x and y slabs then depend on
-                                //         the column only and the z slab on the row only (same operations, same order: bit-exact decisions)
-                                unsigned mask = 0;
+                                //         the column only and the z slab on the row only.  That form rounds differently from the reference's
+                                //         (b - o) * (1 / (d + 1e-8)): each slab value carries a relative error <= k (roundings + the 1e-8 of the
+                                //         reference's reciprocal, which grows with 1 / |d_axis|; transient_narrow.cu has the derivation), so
+                                //         candidates with |tmax - tmin| <= 2.5 k |tmax| (all of a block with k > 0.05) are decided again by the
+                                //         reference's own expression (ray_aabb_x): bit-exact hit masks
+                                unsigned mask = 0, border = 0;
                                 const int ni = min(4, i1 - ib + 1), nj = min(8, j1 - jb + 1);
                                 // (columns in two halves of 4: footprints are rarely wider, the second half is skipped by a branch)
 #pragma unroll
                                 for (int jh = 0; jh < 8; jh += 4) {
                                     if (jh < nj) {
                                         float xymn[4], xymx[4];
+                                        float kmx = 0.f;
 #pragma unroll
                                         for (int jj = 0; jj < 4; ++jj) {
                                             xymn[jj] = INFINITY; xymx[jj] = -INFINITY;
@@ -586,8 +503,14 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                                 const float tx0 = lox * icp, tx1 = hix * icp, ty0 = loy * isp, ty1 = hiy * isp;
                                                 xymn[jj] = fmaxf(fminf(tx0, tx1), fminf(ty0, ty1));
                                                 xymx[jj] = fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1));
+                                                kmx = fmaxf(kmx, fmaxf(fabsf(icp), fabsf(isp)));
                                             }
                                         }
+#pragma unroll
+                                        for (int ii = 0; ii < 4; ++ii)
+                                            if (ii < ni) kmx = fmaxf(kmx, fabsf(thb[ii * 96 + TH_TAN]));
+                                        const float kblk = fmaf(kmx, kband, 1e-6f), kk = 2.5f * kblk;
+                                        const bool allb = kblk > 0.05f;
 #pragma unroll
                                         for (int ii = 0; ii < 4; ++ii) {
                                             if (ii < ni) {
@@ -598,20 +521,48 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                                 for (int jj = 0; jj < 4; ++jj) {
                                                     const float tmin = fmaxf(xymn[jj], zmn);
                                                     const float tmax = fminf(xymx[jj], zmx);
-                                                    const bool hit = (tmax >= tmin) && (tmax >= 0.f);
+                                                    const float diff = tmax - tmin;
+                                                    const bool hit = (diff >= 0.f) && (tmax >= 0.f);
+                                                    const bool bd = (jh + jj < nj) && (allb || fabsf(diff) <= kk * fabsf(tmax));
                                                     mask |= (hit ? 1u : 0u) << (ii * 8 + jh + jj);
-                                                    if (MODE == MODE_COUNT && hit) {
-                                                        // slab interval stretched about its midpoint by 5.3/3 (t = t'/sin(theta))
-                                                        const float ist = 1.0f / thb[ii * 96 + TH_SIN];
-                                                        const float mid = 0.5f * (tmin + tmax) * ist, half = 0.5f * (tmax - tmin) * ist * (5.3f / 3.0f);
-                                                        const int ka = clamp_ceil((mid - half - t0) * inv_dt, s_lo, s_hi + 1),
-                                                                  kb = clamp_floor((mid + half - t0) * inv_dt, s_lo - 1, s_hi);
-                                                        c_hits += (r_in <= mid && mid < r_out) ? 1 : 0;
-                                                        if (kb >= ka) { c_ws += kb - ka + 1; wb_lo = min(wb_lo, ka); wb_hi = max(wb_hi, kb); }
-                                                    }
+                                                    border |= (bd ? 1u : 0u) << (ii * 8 + jh + jj);
                                                 }
                                             }
                                         }
+                                    }
+                                }
+                                while (border) {
+                                    const int bb = __ffs(border) - 1;
+                                    border &= border - 1;
+                                    const float* const thp = thb + (bb >> 3) * 96;
+                                    const float* const php = phb + (bb & 7) * 128;
+                                    const float box[6] = {v3.y, v3.z, v3.w, v4.x, v4.y, v4.z};
+                                    const bool h = ray_aabb_x(ox, oy, oz, __fmul_rn(thp[TH_SIN], php[PH_COS]), __fmul_rn(thp[TH_SIN], php[PH_SIN]), thp[TH_COS], box);
+                                    mask = h ? (mask | (1u << bb)) : (mask & ~(1u << bb));
+                                }
+                                if (P.hit_dump) {      // (tests only) dense membership [scan point][ray][Gaussian], compared bit for bit with the reference's filter lists
+                                    for (unsigned m = mask; m; m &= m - 1) {
+                                        const int bb = __ffs(m) - 1;
+                                        const size_t ray = (size_t)(ib + (bb >> 3)) * A + jb + (bb & 7);
+                                        P.hit_dump[(((size_t)tile * NLOS_TILE + lane) * A * A + ray) * P.N + (ent & ((1u << NLOS_ENTRY_SHIFT) - 1u))] = 1;
+                                    }
+                                }
+                                if (MODE == MODE_COUNT) {
+                                    for (unsigned m = mask; m; m &= m - 1) {
+                                        const int bb = __ffs(m) - 1;
+                                        const float* const thp = thb + (bb >> 3) * 96;
+                                        const float* const php = phb + (bb & 7) * 128;
+                                        const float icp = php[PH_ICOS], isp = php[PH_ISIN], tth = thp[TH_TAN];
+                                        const float tx0 = lox * icp, tx1 = hix * icp, ty0 = loy * isp, ty1 = hiy * isp, tz0 = loz * tth, tz1 = hiz * tth;
+                                        const float tmin = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fminf(tz0, tz1));
+                                        const float tmax = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fmaxf(tz0, tz1));
+                                        // slab interval stretched about its midpoint by 5.3/3 (t = t'/sin(theta))
+                                        const float ist = 1.0f / thp[TH_SIN];
+                                        const float mid = 0.5f * (tmin + tmax) * ist, half = 0.5f * (tmax - tmin) * ist * (5.3f / 3.0f);
+                                        const int ka = clamp_ceil((mid - half - t0) * inv_dt, s_lo, s_hi + 1),
+                                                  kb = clamp_floor((mid + half - t0) * inv_dt, s_lo - 1, s_hi);
+                                        c_hits += (r_in <= mid && mid < r_out) ? 1 : 0;
+                                        if (kb >= ka) { c_ws += kb - ka + 1; wb_lo = min(wb_lo, ka); wb_hi = max(wb_hi, kb); }
                                     }
                                 }
                                 // ---- 2. consume the hits.  Rays the recurrence cannot carry (seed not representable, narrower than a bin;
@@ -899,22 +850,10 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
     }
 }
 
-static size_t transient_smem_bytes(int A, int window)
-{
-    size_t f = (size_t)(NLOS_NTAB * A + NLOS_PINFO_ROWS) * NLOS_TILE + (size_t)TR_WPB * (window + 2 * TR_GUARD) * NLOS_TILE +
-               (size_t)TR_WPB * TR_STAGES * TR_RING * NLOS_REC_FLOATS;
-    return f * 4 + (1 + TR_WPB * TR_STAGES) * 8 + 32;
-}
-
 template <int MODE, bool BWD>
 static int launch_transient(const TransientParams& P, cudaStream_t s, const char* name)
 {
-    static int n_sm = 0;
-    if (n_sm == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sm <= 0) n_sm = 148;
-    }
+    int n_sm = transient_num_sms();
     cudaError_t em = cudaMemsetAsync(P.work, 0, (size_t)P.n_tiles * sizeof(int), s);
     NLOS_REQUIRE(em == cudaSuccess, "%s: memset: %s", name, cudaGetErrorString(em));
     size_t smem = transient_smem_bytes(P.A, P.window);
@@ -926,78 +865,96 @@ static int launch_transient(const TransientParams& P, cudaStream_t s, const char
     return 0;
 }
 
+static unsigned char* g_hit_dump = nullptr;
+// tests only: while set, every render launch also marks the (scan point, ray, Gaussian) triples that pass its slab test in the dense byte
+// array hits [n_tiles*32][A*A][N] (caller zeroes); pass NULL to switch the dump off again
+extern "C" int nlosb200_debug_hit_dump(unsigned char* hits) { g_hit_dump = hits; return 0; }
+
 static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                       const int* list_bins,
-                       const long long* cell_offsets, int* work, float t0, float dt, int T, int window, int bucket, int slice_len,
-                       float c_deltaT, float mcut, int mode)
+                       const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls, int* work, float t0,
+                       float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, int variant)
 {
     NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && A >= 1 && A <= 128, "transient: bad sizes");
     NLOS_REQUIRE(window >= 32 && window % 8 == 0 && bucket >= 1 && (bucket & (bucket - 1)) == 0 && 2 * bucket <= window && slice_len > 0,
                  "transient: bad window/bucket/slice_len (bucket must be a power of two)");
     NLOS_REQUIRE(mode == MODE_NUM || mode == MODE_ANA, "transient: mode must be 0 (numerical) or 1 (analytic-exact)");
+    NLOS_REQUIRE(variant == 0 || variant == 1, "transient: variant must be 0 (register accumulators) or 1 (direct to window)");
+    NLOS_REQUIRE(n_classes >= 1 && n_classes <= 2 && cls >= 0 && cls < n_classes, "transient: class %d of %d", cls, n_classes);
     NLOS_REQUIRE(tiles && records && list && list_bins && cell_offsets && work, "transient: null pointer");
     NLOS_REQUIRE(T <= 65535, "transient: T=%d > 65535", T);
     NLOS_REQUIRE(((uintptr_t)tiles % 16) == 0 && ((uintptr_t)records % 16) == 0, "transient: tiles/records must be 16-byte aligned");
     P.tiles = tiles; P.n_tiles = n_tiles; P.A = A; P.records = records; P.N = N; P.list = reinterpret_cast<const unsigned*>(list);
     P.list_bins = reinterpret_cast<const unsigned*>(list_bins);
+    P.list_capacity = list_capacity;
     P.cell_offsets = cell_offsets; P.work = work;
     P.t0 = t0; P.dt = dt; P.inv_dt = 1.0f / dt; P.T = T; P.window = window; P.bucket = bucket; P.n_buckets = (T + bucket - 1) / bucket;
+    P.cpt = n_classes * P.n_buckets; P.cell0 = cls * P.n_buckets;
     P.slice_len = slice_len; P.flush_scale = mode == MODE_NUM ? c_deltaT : 1.0f; P.mcut2 = mcut * mcut;
-    P.H = nullptr; P.gH = nullptr; P.dacc = nullptr; P.counters = nullptr;
+    P.H = nullptr; P.gH = nullptr; P.dacc = nullptr; P.counters = nullptr; P.hit_dump = g_hit_dump;
     return 0;
 }
 
 extern "C" int nlosb200_transient_warps_per_block(void) { return TR_WPB; }
 
 extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                          const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
-                                          int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, float* H, void* stream)
+                                          const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
+                                          int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
+                                          int mode, int variant, int accumulate, float* H, void* stream)
 {
     TransientParams P;
-    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, cell_offsets, work, t0, dt, T, window, bucket, slice_len, c_deltaT, mcut,
-                         mode);
+    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
+                         bucket, slice_len, c_deltaT, mcut, mode, variant);
     if (rc) return rc;
     NLOS_REQUIRE(H, "transient_forward: null H");
     cudaStream_t s = (cudaStream_t)stream;
-    cudaError_t e = cudaMemsetAsync(H, 0, (size_t)n_tiles * NLOS_TILE * T * sizeof(float), s);
-    NLOS_REQUIRE(e == cudaSuccess, "transient_forward: memset: %s", cudaGetErrorString(e));
+    if (!accumulate) {
+        cudaError_t e = cudaMemsetAsync(H, 0, (size_t)n_tiles * NLOS_TILE * T * sizeof(float), s);
+        NLOS_REQUIRE(e == cudaSuccess, "transient_forward: memset: %s", cudaGetErrorString(e));
+    }
     P.H = H;
+    if (variant == 1) return launch_transient_narrow(P, mode, false, s);
     return mode == MODE_NUM ? launch_transient<MODE_NUM, false>(P, s, "transient_kernel<num,fwd>")
                             : launch_transient<MODE_ANA, false>(P, s, "transient_kernel<ana,fwd>");
 }
 
 extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                           const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
-                                           int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, const float* grad_H,
-                                           float* dacc, void* stream)
+                                           const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
+                                           int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
+                                           int mode, int variant, int accumulate, const float* grad_H, float* dacc, void* stream)
 {
     TransientParams P;
-    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, cell_offsets, work, t0, dt, T, window, bucket, slice_len, c_deltaT, mcut,
-                         mode);
+    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
+                         bucket, slice_len, c_deltaT, mcut, mode, variant);
     if (rc) return rc;
     NLOS_REQUIRE(grad_H && dacc, "transient_backward: null pointer");
     cudaStream_t s = (cudaStream_t)stream;
-    cudaError_t e = cudaMemsetAsync(dacc, 0, (size_t)N * NLOS_GRAD_FLOATS * sizeof(float), s);
-    NLOS_REQUIRE(e == cudaSuccess, "transient_backward: memset: %s", cudaGetErrorString(e));
+    if (!accumulate) {
+        cudaError_t e = cudaMemsetAsync(dacc, 0, (size_t)N * NLOS_GRAD_FLOATS * sizeof(float), s);
+        NLOS_REQUIRE(e == cudaSuccess, "transient_backward: memset: %s", cudaGetErrorString(e));
+    }
     P.gH = grad_H;
     P.dacc = dacc;
+    if (variant == 1) return launch_transient_narrow(P, mode, true, s);
     return mode == MODE_NUM ? launch_transient<MODE_NUM, true>(P, s, "transient_kernel<num,bwd>")
                             : launch_transient<MODE_ANA, true>(P, s, "transient_kernel<ana,bwd>");
 }
 
 // work counters of SURVEY.md 8(d): counters[0] hit (g,ray) pairs, [1] W_s, [2] sample-evals this library evaluates, [3] W_b
 extern "C" int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
-                                        const int* list_bins, const long long* cell_offsets, int* work, float t0, float dt, int T,
-                                        int window, int bucket, int slice_len, float mcut, unsigned long long* counters, void* stream)
+                                        const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
+                                        int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float mcut, int accumulate,
+                                        unsigned long long* counters, void* stream)
 {
     TransientParams P;
-    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, cell_offsets, work, t0, dt, T, window, bucket, slice_len, 1.0f, mcut,
-                         MODE_NUM);
+    int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
+                         bucket, slice_len, 1.0f, mcut, MODE_NUM, 0);
     if (rc) return rc;
     NLOS_REQUIRE(counters, "transient_count: null counters");
     cudaStream_t s = (cudaStream_t)stream;
-    cudaError_t e = cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), s);
-    NLOS_REQUIRE(e == cudaSuccess, "transient_count: memset: %s", cudaGetErrorString(e));
+    if (!accumulate) {
+        cudaError_t e = cudaMemsetAsync(counters, 0, 4 * sizeof(unsigned long long), s);
+        NLOS_REQUIRE(e == cudaSuccess, "transient_count: memset: %s", cudaGetErrorString(e));
+    }
     P.counters = counters;
     return launch_transient<MODE_COUNT, false>(P, s, "transient_kernel<count>");
 }

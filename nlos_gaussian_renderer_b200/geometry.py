@@ -28,17 +28,16 @@ def volume_box_point(volume_position, volume_size):
 
 
 def torch_linspace_rows(lo, hi, steps):
-    """Row-wise torch.linspace(lo[i], hi[i], steps) in fp32 with torch's own two-sided formula
-    (start + i*step for the lower half, end - (steps-1-i)*step for the upper half)."""
-    lo = lo.to(torch.float32).reshape(-1, 1)
-    hi = hi.to(torch.float32).reshape(-1, 1)
-    if steps == 1:
-        return lo.clone()
-    step = (hi - lo) / float(steps - 1)
-    idx = torch.arange(steps, device=lo.device, dtype=torch.float32).reshape(1, -1)
-    lower = lo + step * idx
-    upper = hi - step * (float(steps - 1) - idx)
-    return torch.where(idx < steps / 2, lower, upper)
+    """Row i = torch.linspace(lo[i], hi[i], steps, dtype=float32) on lo's device, through torch.linspace ITSELF, one call per row with the
+    bounds as Python floats -- exactly what the reference does per scan point (nlos_helpers.py:159-160 after the .item() calls of :153-156).
+    A closed-form restatement is not bit-stable: torch's CPU kernel evaluates (start + step * i0) + step * j per SIMD chunk and its CUDA
+    kernel contracts start + step * i into one FMA, so the last bit of a lattice angle depends on the device the lattice is built on
+    (tests/test_ref_python.py pins this function against the reference's own output).  Host-side, once per scan grid."""
+    dev = lo.device
+    lo_l, hi_l = lo.detach().to("cpu", torch.float32).tolist(), hi.detach().to("cpu", torch.float32).tolist()
+    if not lo_l:
+        return torch.empty(0, steps, dtype=torch.float32, device=dev)
+    return torch.stack([torch.linspace(a, b, steps, dtype=torch.float32, device=dev) for a, b in zip(lo_l, hi_l)])
 
 
 class ScanGeometry:
@@ -149,9 +148,7 @@ class ScanGeometry:
         return out.contiguous()
 
     def slab(self, rank, world):
-        """Contiguous slab of scan rows for one rank (rows split at tile_y granularity)."""
-        nty = -(-self.Sy // self.tile_y)
-        per = -(-nty // world)
-        y0 = min(rank * per * self.tile_y, self.Sy)
-        y1 = min((rank + 1) * per * self.tile_y, self.Sy)
-        return y0, y1
+        """Contiguous slab of scan rows [y0, y1) of one rank: parallel.slab_rows (the ONE definition bench.py, the tests and
+        gather_transient share)."""
+        from .parallel import slab_rows
+        return slab_rows(self.Sy, self.tile_y, rank, world)

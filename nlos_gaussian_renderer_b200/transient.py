@@ -14,25 +14,37 @@ from . import _lib
 from .geometry import ScanGeometry, TILE
 
 MODES = {"numerical": 0, "analytic": 1, "analytic_exact": 1}
-N_SM = 148                    # B200
+VARIANTS = {"wide": 0, "narrow": 1, "auto": 2}
 
 
 def _f32c(t):
-    assert t.is_cuda, "libnlosb200 needs CUDA tensors (there is no CPU fallback)"
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise RuntimeError("libnlosb200 needs CUDA tensors (there is no CPU fallback)")
+    if not t.dtype.is_floating_point:
+        raise RuntimeError(f"expected a floating-point tensor, got {t.dtype}")
     return t.detach().to(torch.float32).contiguous()
+
+
+class ListOverflow(RuntimeError):
+    """The entry lists of a step did not fit the list buffer (the step rendered nothing); the buffer has been regrown."""
 
 
 class TransientRenderer:
     """Stateful renderer for one ScanGeometry: owns the preprocess / binning workspaces."""
 
     def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
-                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0):
+                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=2.5):
         """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
         (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries a warp pulls at a time from its
-        tile's counter (default: 16..256, sized so that every warp of the persistent grid gets >= 32 slices)."""
+        tile's counter (default: 16..256, sized so that every warp of the persistent grid gets >= 32 slices).
+        variant: which scan-tile kernel renders an entry -- "wide" (register accumulators, transient.cu), "narrow" (direct to window,
+        transient_narrow.cu) or "auto": per (tile, Gaussian) entry at binning time, narrow when the Gaussian's 3-sigma AABB spans at most
+        `narrow_rays` lattice pitches (the two kernels give the same result, they differ in speed only)."""
         self.geom = geom
         self.T, self.t0, self.dt, self.c_deltaT = int(T), float(t0), float(dt), float(c_deltaT)
         self.mode = MODES[mode] if isinstance(mode, str) else int(mode)
+        self.variant = VARIANTS[variant] if isinstance(variant, str) else int(variant)
+        self.narrow_rays = float(narrow_rays)
         self.window = int(window)
         if bucket is None:
             bucket = 8
@@ -43,17 +55,19 @@ class TransientRenderer:
         self.slice_len = slice_len
         self.mcut, self.mod, self.sigma = float(mcut), float(scaling_modifier), float(sigma_bbox)
         self.wpb = _lib.lib().nlosb200_transient_warps_per_block()
+        self.n_classes = 2 if self.variant == 2 else 1
         self._N = None
         self._list = None
+        self._pending = None           # (pinned header copy, event) of the previous prepare(): checked lazily, no host sync per step
+        self.generation = 0            # incremented by every prepare(): a backward must see the lists of ITS forward
         self.last_total = 0
-        self.n_items = 0
 
     # ------------------------------------------------------------------------------------------
     def _alloc(self, N, dev):
         if self._N == N:
             return
         L = _lib.lib()
-        n_cells = self.geom.n_tiles * self.n_buckets
+        n_cells = self.geom.n_tiles * self.n_buckets * self.n_classes
         self.records = torch.empty(N * L.nlosb200_record_floats() + 32, dtype=torch.float32, device=dev)
         off = ((-self.records.data_ptr()) % 128) // 4         # 128-byte alignment for the TMA gather
         self.records = self.records[off: off + N * L.nlosb200_record_floats()]
@@ -64,13 +78,17 @@ class TransientRenderer:
         self.tile_items = torch.empty(self.geom.n_tiles + 1, dtype=torch.int32, device=dev)
         self.work = torch.empty(self.geom.n_tiles, dtype=torch.int32, device=dev)      # per-tile slice counters (work stealing)
         self.header = torch.zeros(4, dtype=torch.int64, device=dev)
+        self.header_host = torch.zeros(4, dtype=torch.int64).pin_memory()
         self.dacc = torch.empty(N, L.nlosb200_grad_floats(), dtype=torch.float32, device=dev)
         self._N = N
+        self._list = None
+        self._pending = None
+        n_sm = torch.cuda.get_device_properties(dev).multi_processor_count
         if self.slice_len is None:
             est = self.geom.n_tiles * N * 1.05                    # ~one entry per (tile, Gaussian)
             # >= 32 slices per warp (fine-grained stealing); small scenes go down to 2 entries per slice so that every warp of the
             # grid gets work (cfg1, 8 tiles x 1000 entries: 16 -> 2 entries per slice took the kernels from 1.6 / 3.5 ms to 0.44 / 0.77 ms)
-            self._slice = int(min(256, max(2, est / (N_SM * self.wpb * 32))))
+            self._slice = int(min(256, max(2, est / (n_sm * self.wpb * 32))))
             if self._slice >= 4:
                 self._slice = self._slice // 4 * 4
         else:
@@ -78,64 +96,113 @@ class TransientRenderer:
 
     def _bin_args(self):
         g = self.geom
-        return (g.tiles().data_ptr(), g.n_tiles, g.A, self.shell.data_ptr(), self._N, self.t0, self.dt, self.T, self.window, self.bucket)
+        return (g.tiles().data_ptr(), g.n_tiles, g.A, self.shell.data_ptr(), self._N, self.t0, self.dt, self.T, self.window, self.bucket,
+                self.n_classes)
+
+    def _check_pending(self):
+        """Lazy overflow check of the PREVIOUS prepare(): its header copy finished long ago, so this does not stall the stream."""
+        if self._pending is None:
+            return
+        ev, gen = self._pending
+        self._pending = None
+        ev.synchronize()
+        total, overflow = int(self.header_host[0]), int(self.header_host[2])
+        self.last_total = total
+        if overflow or total > self._list.numel():
+            self._grow(total)
+            raise ListOverflow(f"the entry lists of step {gen} ({total} entries) did not fit the list buffer: that step rendered nothing; "
+                               "the buffer has been regrown, repeat the step")
+
+    def _grow(self, total):
+        dev = self.records.device
+        self._list = torch.empty(max(int(total * 1.25) + 1024, 1024), dtype=torch.int32, device=dev)
+        self._list_bins = torch.empty_like(self._list)                # per entry: shell klo | khi << 16
 
     def prepare(self, means, log_scales, rotations, opacities, features):
-        """preprocess + shell binning for the current parameters (stream ordered; ONE 16-byte readback
-        to size the list buffer and the launch grid)."""
+        """preprocess + shell binning for the current parameters.  Stream ordered: the first call sizes the list buffer with one 32-byte
+        readback; later calls reuse the buffer (25 % head-room over the last known total) and read the header back asynchronously --
+        an overflow is detected one call later (ListOverflow) and by check_lists()."""
         means, log_scales, rotations = _f32c(means), _f32c(log_scales), _f32c(rotations)
         opacities, features = _f32c(opacities).reshape(-1), _f32c(features)
         N = means.shape[0]
         features = features.reshape(N, -1)
-        self._params = (means, log_scales, rotations, opacities, features)
         self._alloc(N, means.device)
+        self._check_pending()
+        self._params = (means, log_scales, rotations, opacities, features)
+        self.generation += 1
         st = _lib.stream()
         _lib.call("nlosb200_preprocess", means.data_ptr(), log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(),
                   features.data_ptr(), N, features.shape[1], self.mod, self.sigma, self.mcut, self.records.data_ptr(),
                   self.shell.data_ptr(), None, st)
-        _lib.call("nlosb200_bin_window_plan", *self._bin_args(), self._slice, self.wpb, self.chunk_counts.data_ptr(),
-                  self.cell_counts.data_ptr(), self.cell_offsets.data_ptr(), self.tile_items.data_ptr(), self.header.data_ptr(), st)
-        hdr = self.header.cpu()
-        total, self.n_items = int(hdr[0]), int(hdr[1])
-        self.last_total = total
-        if self._list is None or self._list.numel() < total:
-            self._list = torch.empty(max(int(total * 1.25), 1024), dtype=torch.int32, device=means.device)
-            self._list_bins = torch.empty_like(self._list)                # per entry: shell klo | khi << 16
-        _lib.call("nlosb200_bin_window_fill", *self._bin_args(), self.chunk_counts.data_ptr(), self.cell_offsets.data_ptr(),
-                  self._list.data_ptr(), self._list_bins.data_ptr(), self._list.numel(), self.header.data_ptr(), st)
+        _lib.call("nlosb200_bin_window_plan", *self._bin_args(), self.narrow_rays if self.variant == 2 else 0.0, self.mcut, self._slice, self.wpb,
+                  self.chunk_counts.data_ptr(), self.cell_counts.data_ptr(), self.cell_offsets.data_ptr(), self.tile_items.data_ptr(),
+                  self.header.data_ptr(), st)
+        if self._list is None:
+            total = int(self.header.cpu()[0])                 # first call only: size the list buffer
+            self.last_total = total
+            self._grow(total)
+        _lib.call("nlosb200_bin_window_fill", *self._bin_args(), self.narrow_rays if self.variant == 2 else 0.0, self.mcut,
+                  self.chunk_counts.data_ptr(),
+                  self.cell_offsets.data_ptr(), self._list.data_ptr(), self._list_bins.data_ptr(), self._list.numel(), self.header.data_ptr(), st)
+        self.header_host.copy_(self.header, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._pending = (ev, self.generation)
 
-    def _render_args(self):
+    def check_lists(self):
+        """Block until the last prepare() is known to have fitted its lists (raises ListOverflow otherwise) -> total entries."""
+        self._check_pending()
+        return self.last_total
+
+    def _launches(self):
+        """(cls, variant) of the render launches: one per entry class."""
+        if self.variant == 2:
+            return ((0, 1), (1, 0))           # class 0 = narrow entries -> direct-to-window kernel, class 1 = wide -> register accumulators
+        return ((0, self.variant),)
+
+    def _render_args(self, cls):
         g = self.geom
         return (g.tiles().data_ptr(), g.n_tiles, g.A, self.records.data_ptr(), self._N, self._list.data_ptr(),
-                self._list_bins.data_ptr(), self.cell_offsets.data_ptr(), self.work.data_ptr(), self.t0, self.dt, self.T, self.window, self.bucket, self._slice)
+                self._list_bins.data_ptr(), self._list.numel(), self.cell_offsets.data_ptr(), self.n_classes, cls, self.work.data_ptr(),
+                self.t0, self.dt, self.T, self.window, self.bucket, self._slice)
 
     def forward_tiled(self):
         """-> H [n_tiles*32, T] in tile-major scan order (after prepare())."""
         H = torch.empty(self.geom.n_tiles * TILE, self.T, dtype=torch.float32, device=self.records.device)
-        _lib.call("nlosb200_transient_forward", *self._render_args(), self.c_deltaT, self.mcut, self.mode, H.data_ptr(), _lib.stream())
+        for n, (cls, var) in enumerate(self._launches()):
+            _lib.call("nlosb200_transient_forward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, int(n > 0), H.data_ptr(),
+                      _lib.stream())
         return H
 
     def forward(self, means, log_scales, rotations, opacities, features):
         self.prepare(means, log_scales, rotations, opacities, features)
         return self.geom.untile(self.forward_tiled())
 
+    def render_backward(self, gH_tiled):
+        """transient backward kernels only: dL/dH (tile-major) -> the packed [N,16] gradient buffer self.dacc."""
+        gH_tiled = _f32c(gH_tiled)
+        for n, (cls, var) in enumerate(self._launches()):
+            _lib.call("nlosb200_transient_backward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, int(n > 0),
+                      gH_tiled.data_ptr(), self.dacc.data_ptr(), _lib.stream())
+        return self.dacc
+
+    def chain(self, params=None):
+        """per-Gaussian chain rule: self.dacc -> (d_means, d_log_scales, d_rotations, d_opacities, d_features)."""
+        means, log_scales, rotations, opacities, features = params if params is not None else self._params
+        outs = [torch.empty_like(means), torch.empty_like(log_scales), torch.empty_like(rotations), torch.empty_like(opacities),
+                torch.empty_like(features)]
+        _lib.call("nlosb200_preprocess_backward", log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(), features.data_ptr(),
+                  self._N, features.shape[1], self.mod, self.dacc.data_ptr(), *[o.data_ptr() for o in outs], 0, _lib.stream())
+        return tuple(outs)
+
     def backward_tiled(self, gH_tiled, reduce_fn=None):
         """dL/dH (tile-major) -> (d_means, d_log_scales, d_rotations, d_opacities, d_features).
         reduce_fn(dacc) runs between the render backward and the per-Gaussian chain: the multi-GPU path
         all-reduces the packed [N,16] buffer there (ONE NCCL all-reduce per fitting step)."""
-        means, log_scales, rotations, opacities, features = self._params
-        N = self._N
-        gH_tiled = _f32c(gH_tiled)
-        st = _lib.stream()
-        _lib.call("nlosb200_transient_backward", *self._render_args(), self.c_deltaT, self.mcut, self.mode, gH_tiled.data_ptr(),
-                  self.dacc.data_ptr(), st)
+        self.render_backward(gH_tiled)
         if reduce_fn is not None:
             reduce_fn(self.dacc)
-        outs = [torch.empty_like(means), torch.empty_like(log_scales), torch.empty_like(rotations), torch.empty_like(opacities),
-                torch.empty_like(features)]
-        _lib.call("nlosb200_preprocess_backward", log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(), features.data_ptr(),
-                  N, features.shape[1], self.mod, self.dacc.data_ptr(), *[o.data_ptr() for o in outs], 0, st)
-        return tuple(outs)
+        return self.chain()
 
     def backward(self, gH, reduce_fn=None):
         return self.backward_tiled(self.geom.tile_grad(gH), reduce_fn)
@@ -144,7 +211,8 @@ class TransientRenderer:
         """Fused  loss = inv_numel * sum (H - target)^2  and  dL/dH = 2 inv_numel (H - target)  on the tile-major layout
         (csrc/loss.cu; the batched counterpart of nlos_helpers.py:280-346).  -> (loss 0-d float64 tensor, dL/dH tile-major or None)."""
         H_tiled, target_tiled = _f32c(H_tiled), _f32c(target_tiled)
-        assert H_tiled.shape == target_tiled.shape
+        if H_tiled.shape != target_tiled.shape:
+            raise RuntimeError(f"H {tuple(H_tiled.shape)} and target {tuple(target_tiled.shape)} differ in shape")
         loss = torch.zeros((), dtype=torch.float64, device=H_tiled.device)
         gH = torch.empty_like(H_tiled) if want_grad else None
         _lib.call("nlosb200_mse_loss_grad", H_tiled.data_ptr(), target_tiled.data_ptr(), H_tiled.numel(), float(inv_numel),
@@ -154,29 +222,38 @@ class TransientRenderer:
     def count_work(self):
         """SURVEY.md 8(d) work counters for the prepared scene (dict)."""
         c = torch.zeros(4, dtype=torch.int64, device=self.records.device)
-        _lib.call("nlosb200_transient_count", *self._render_args(), self.mcut, c.data_ptr(), _lib.stream())
+        for cls in range(self.n_classes):
+            _lib.call("nlosb200_transient_count", *self._render_args(cls), self.mcut, int(cls > 0), c.data_ptr(), _lib.stream())
         c = c.cpu().tolist()
         return {"hits": c[0], "W_s": c[1], "evals": c[2], "W_b": c[3]}
 
     def lists(self):
         """(cell_counts, cell_offsets, list) as CPU numpy arrays -- for the bit-exact binning tests."""
-        total = self.last_total
+        total = self.check_lists()
         import numpy as np
         return (self.cell_counts.cpu().numpy(), self.cell_offsets.cpu().numpy(), self._list[:total].cpu().numpy().view(np.uint32))
 
 
 class _TransientFn(torch.autograd.Function):
-    """autograd boundary, same role as CUDARenderFunction (gaussian_model/cuda_autograd.py:18-191)."""
+    """autograd boundary, same role as CUDARenderFunction (gaussian_model/cuda_autograd.py:18-191).  The five parameter tensors are
+    saved on ctx (an in-place update between forward and backward trips autograd's version check); the binning state lives on the
+    renderer, so a backward whose renderer has since prepared another scene re-runs prepare() from the saved tensors first."""
 
     @staticmethod
     def forward(ctx, renderer, means, log_scales, rotations, opacities, features):
+        out = renderer.forward(means, log_scales, rotations, opacities, features)
         ctx.renderer = renderer
+        ctx.generation = renderer.generation
         ctx.shapes = (opacities.shape, features.shape)
-        return renderer.forward(means, log_scales, rotations, opacities, features)
+        ctx.save_for_backward(means, log_scales, rotations, opacities, features)
+        return out
 
     @staticmethod
     def backward(ctx, gH):
         r = ctx.renderer
+        if r.generation != ctx.generation:          # another forward()/prepare() ran on this renderer since: rebuild this call's lists
+            r.prepare(*ctx.saved_tensors)
+            ctx.generation = r.generation
         dm, ds, dr, do, df = r.backward(gH)
         return None, dm, ds, dr, do.reshape(ctx.shapes[0]), df.reshape(ctx.shapes[1])
 

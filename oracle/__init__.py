@@ -194,22 +194,56 @@ def shell_bins(scan_o, Sy, Sx, tile_y, tile_x, means, log_scales, scaling_modifi
 ENTRY_SHIFT = 26      # list entry = gaussian id | (sub-interval index << 26)
 
 
-def window_lists(klo, khi, T, window, bucket):
+def entry_classes(scan_o, valid, lattice_step, Sy, Sx, tile_y, tile_x, means, log_scales, scaling_modifier, mcut, klo, khi, window, bucket,
+                  narrow_rays, exp_mode=1):
+    """DEFINITION of the entry classes of the window binning (csrc/binning.cu header): class 0 ("narrow") when the Gaussian is listed once
+    in the tile (khi - klo + 1 <= L) and  (6 / mcut) rad <= (narrow_rays * pitch) * sqrt(d2min)  in single-rounded fp32, with
+    rad = mcut * max(scale), pitch = min over the tile's valid scan points of lattice_step (= min(dtheta, dphi), 0 where the lattice is
+    unusable) and d2min = min over the tile's valid scan points of |mu - o|^2 (summed as ((dx^2 + dy^2) + dz^2)); else class 1.
+    scan_o [Sy*Sx,3], lattice_step [Sy*Sx] -> int32 [n_tiles, N]."""
+    f = np.float32
+    scan_o, means, log_scales = _f(scan_o).reshape(Sy, Sx, 3), _f(means), _f(log_scales)
+    step = _f(lattice_step).reshape(Sy, Sx)
+    N = means.shape[0]
+    nty, ntx = -(-Sy // tile_y), -(-Sx // tile_x)
+    L = window - bucket
+    s = det_expf(log_scales) if exp_mode == 1 else np.exp(log_scales).astype(f)
+    s = (s * f(scaling_modifier)).astype(f)
+    rad = (f(mcut) * s.max(1)).astype(f)
+    lhs = (rad * (f(6.0) / f(mcut))).astype(f)
+    out = np.ones((nty * ntx, N), np.int32)
+    for ty in range(nty):
+        for tx in range(ntx):
+            o = scan_o[ty * tile_y:(ty + 1) * tile_y, tx * tile_x:(tx + 1) * tile_x].reshape(-1, 3)
+            st = step[ty * tile_y:(ty + 1) * tile_y, tx * tile_x:(tx + 1) * tile_x].reshape(-1)
+            d = (means[:, None, :] - o[None, :, :]).astype(f)
+            d2 = ((d[..., 0] * d[..., 0]).astype(f) + (d[..., 1] * d[..., 1]).astype(f)).astype(f)
+            d2 = (d2 + (d[..., 2] * d[..., 2]).astype(f)).astype(f)
+            rhs = ((f(narrow_rays) * st.min()).astype(f) * np.sqrt(d2.min(1)).astype(f)).astype(f)
+            t = ty * ntx + tx
+            out[t] = np.where((khi[t] - klo[t] + 1 <= L) & (lhs <= rhs), 0, 1)
+    return out
+
+
+def window_lists(klo, khi, T, window, bucket, cls=None):
     """DEFINITION of the window-binning lists the batched renderer consumes.  A Gaussian whose tile-level shell is
     [klo, khi] contributes entries e = 0 .. ceil(len/L)-1 with L = window - bucket; entry e covers bins
     [klo + e L, min(khi, klo + (e+1) L - 1)] and lives in cell (tile, (klo + e L) // bucket).  Per cell the entries are
-    ascending in the Gaussian id.  -> counts [n_tiles*n_buckets] int32, offsets int64 [cells+1], list uint32."""
+    ascending in the Gaussian id.  With entry classes (cls int [n_tiles, N] of 0 / 1, entry_classes()) the cells of a tile are class-major:
+    cell = tile * 2 n_buckets + cls * n_buckets + bucket.  -> counts [cells] int32, offsets int64 [cells+1], list uint32."""
     klo = np.asarray(klo, np.int64)
     khi = np.asarray(khi, np.int64)
     nt, N = klo.shape
     L = window - bucket
     nb = -(-T // bucket)
+    ncls = 1 if cls is None else 2
     n_e = np.where(klo <= khi, -(-(khi - klo + 1) // L), 0)
     cells, vals = [], []
     for e in range(int(n_e.max()) if n_e.size else 0):
         t, g = np.nonzero(n_e > e)
         s = klo[t, g] + e * L
-        cells.append(t * nb + s // bucket)
+        c = 0 if cls is None else np.asarray(cls, np.int64)[t, g]
+        cells.append(t * (ncls * nb) + c * nb + s // bucket)
         vals.append(g | (e << ENTRY_SHIFT))
     if cells:
         cells, vals = np.concatenate(cells), np.concatenate(vals)
@@ -217,8 +251,8 @@ def window_lists(klo, khi, T, window, bucket):
         cells, vals = cells[order], vals[order]
     else:
         cells, vals = np.zeros(0, np.int64), np.zeros(0, np.int64)
-    counts = np.bincount(cells, minlength=nt * nb).astype(np.int32)
-    offsets = np.zeros(nt * nb + 1, np.int64)
+    counts = np.bincount(cells, minlength=nt * nb * ncls).astype(np.int32)
+    offsets = np.zeros(nt * nb * ncls + 1, np.int64)
     np.cumsum(counts, out=offsets[1:])
     return counts, offsets, vals.astype(np.uint32)
 

@@ -122,7 +122,7 @@ def test_error_convention_without_gpu():
         _C.render_rays(z, z, torch.zeros(5), z, z, torch.zeros(4, 4), torch.zeros(4, 1), torch.zeros(4, 1), torch.zeros(3), 0, 1.0, 0.01,
                        1.0, True, "netf")
     from nlos_gaussian_renderer_b200.transient import _f32c
-    with pytest.raises(AssertionError):
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
         _f32c(z)
-    rc = _lib.lib().nlosb200_bin_window_plan(None, 0, 0, None, 0, 0.0, 1.0, 0, 128, 8, 0, 0, None, None, None, None, None, None)
+    rc = _lib.lib().nlosb200_bin_window_plan(None, 0, 0, None, 0, 0.0, 1.0, 0, 128, 8, 1, 0.0, 5.3, 0, 0, None, None, None, None, None, None)
     assert rc < 0 and b"bad sizes" in _lib.lib().nlosb200_last_error()

@@ -1,0 +1,99 @@
+"""The two scan-tile kernels (transient.cu: register accumulators, transient_narrow.cu: direct to window) and the per-entry choice between
+them ("auto": entry classes decided at binning time) must be interchangeable: same hit masks as the reference's per-ray filter
+(src/ray_aabb.cu:10-61, include/cuda_utils.cuh:97-121) BIT FOR BIT, same histograms and gradients within the fp32 tolerance."""
+import numpy as np
+import pytest
+import torch
+
+from nlos_gaussian_renderer_b200.transient import TransientRenderer, render_transient_batch
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+def _r(geom, ta, mode, **kw):
+    return TransientRenderer(geom, ta["t_samples"].numel(), ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, **kw)
+
+
+@pytest.mark.parametrize("variant", ["wide", "narrow", "auto"])
+@pytest.mark.parametrize("shape,scale_mul", [((150, 5, 9, 48, 6), 1.0), ((300, 6, 7, 64, 12), 0.4), ((200, 4, 8, 64, 9), 2.5), ((64, 3, 5, 40, 3), 6.0),
+                                             ((500, 8, 8, 128, 16), 0.25)])
+def test_hit_masks_equal_the_reference_filter_bit_for_bit(variant, shape, scale_mul):
+    """Every (scan point, ray, Gaussian) triple the render kernel evaluates == the reference's slab test with cap = N
+    (oracle.filter_gaussians, itself pinned bit-exact against the reference source in tests/test_oracle.py)."""
+    N, Sy, Sx, T, A = shape
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=scale_mul, device="cuda")
+    # mcut = 60: no radial reject and every ray of a hit inside the cut, so the dump holds the bare slab-test decisions
+    r = _r(geom, ta, "numerical", variant=variant, mcut=60.0, window=120 if T > 100 else 96)
+    got = util.hit_masks_gpu(r, params)
+    from tests.test_gpu_transient import scenes_cpu
+    want = util.ray_masks(scenes_cpu(geom), [p.cpu() for p in params])
+    # Gaussians the time window does not reach at all are not listed (radial cull of the binning): compare where listed
+    listed = np.zeros((geom.S, N), bool)
+    cnt, off, lst = r.lists()
+    perm = geom.perm.cpu().numpy()
+    cpt = r.n_classes * r.n_buckets
+    for t in range(geom.n_tiles):
+        gs = lst[off[t * cpt]: off[(t + 1) * cpt]] & ((1 << 26) - 1)
+        pts = perm[t * 32:(t + 1) * 32]
+        listed[np.ix_(pts[pts >= 0], gs)] = True
+    assert listed.mean() > 0.5
+    diff = (got != want) & listed[:, None, :]
+    assert want.sum() > 0
+    assert diff.sum() == 0, f"{diff.sum()} of {want.sum()} slab decisions differ from the reference"
+    assert not (got & ~listed[:, None, :]).any()
+
+
+@pytest.mark.parametrize("mode", ["numerical", "analytic"])
+@pytest.mark.parametrize("scale_mul", [0.3, 1.0, 4.0])
+def test_variants_agree(mode, scale_mul):
+    N, Sy, Sx, T, A = 400, 6, 10, 160, 10
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=scale_mul, device="cuda")
+    gH = torch.rand(Sy, Sx, T, generator=torch.Generator().manual_seed(2)).cuda()
+    outs = {}
+    for variant in ("wide", "narrow", "auto"):
+        r = _r(geom, ta, mode, variant=variant, narrow_rays=1.5)
+        ps = [p.clone().requires_grad_() for p in params]
+        H = render_transient_batch(r, *ps)
+        (H * gH).sum().backward()
+        outs[variant] = (H.detach().cpu().numpy(), [p.grad.cpu().numpy() for p in ps])
+    for v in ("narrow", "auto"):
+        assert util.rel_to_max(outs[v][0], outs["wide"][0]) < 2e-5
+        for a, b in zip(outs[v][1], outs["wide"][1]):
+            if np.abs(b).max() > 0:
+                assert util.rel_to_max(a, b) < 3e-5
+
+
+def test_backward_after_another_forward_uses_its_own_lists():
+    """a second forward() on the same renderer before the first graph's backward() must not corrupt the first gradients."""
+    geom, ta, params = util.small_scene(200, 5, 9, 48, 6, device="cuda")
+    r = _r(geom, ta, "numerical")
+    ps = [p.clone().requires_grad_() for p in params]
+    H = render_transient_batch(r, *ps)
+    with torch.no_grad():
+        other = [p[:50].contiguous() for p in params]
+        r.forward(*other)                                   # e.g. a validation render
+    H.sum().backward()
+    ps2 = [p.clone().requires_grad_() for p in params]
+    render_transient_batch(_r(geom, ta, "numerical"), *ps2).sum().backward()
+    for a, b in zip(ps, ps2):
+        assert util.rel_to_max(a.grad.cpu().numpy(), b.grad.cpu().numpy()) < 1e-5
+
+
+def test_list_overflow_is_detected_one_step_later():
+    from nlos_gaussian_renderer_b200.transient import ListOverflow
+    geom, ta, params = util.small_scene(100, 5, 9, 48, 6, device="cuda")
+    r = _r(geom, ta, "numerical")
+    H0 = r.forward(*[p[:10].contiguous() for p in params])          # sizes the list buffer for 10 Gaussians
+    r._N = None                                                      # (new N: workspaces are rebuilt, the list buffer is sized again)
+    H1 = r.forward(*params)
+    assert float(H1.abs().max()) > 0
+    # same N, many more entries than the buffer holds: shrink the buffer by hand
+    r._list = r._list[:8]
+    r._list_bins = r._list_bins[:8]
+    H2 = r.forward(*params)
+    assert float(H2.abs().max()) == 0.0                              # the launch rendered nothing ...
+    with pytest.raises(ListOverflow):
+        r.check_lists()                                              # ... and says so
+    H3 = r.forward(*params)                                          # the buffer has been regrown
+    assert torch.equal(H3, H1) or util.rel_to_max(H3.cpu().numpy(), H1.cpu().numpy()) < 1e-6

@@ -47,3 +47,35 @@ def ray_masks(geom, params):
 def rel_to_max(a, b):
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-300))
+
+
+def oracle_window_lists(geom, ta, params, r):
+    """The oracle's definition of the renderer r's entry lists (counts, offsets, list), with r's entry classes."""
+    T = r.T
+    klo, khi = oracle.shell_bins(np32(geom.scan_o), geom.Sy, geom.Sx, geom.tile_y, geom.tile_x, np32(params[0]), np32(params[1]),
+                                 r.mod, r.mcut, ta["t0"], ta["dt"], T, exp_mode=1)
+    cls = None
+    if r.n_classes == 2:
+        lat = np32(geom.lattice)
+        step = np.minimum(lat[:, 1], lat[:, 3])
+        cls = oracle.entry_classes(np32(geom.scan_o), None, step, geom.Sy, geom.Sx, geom.tile_y, geom.tile_x, np32(params[0]), np32(params[1]),
+                                   r.mod, r.mcut, klo, khi, r.window, r.bucket, r.narrow_rays, exp_mode=1)
+    return oracle.window_lists(klo, khi, T, r.window, r.bucket, cls), cls
+
+
+def hit_masks_gpu(r, params):
+    """[S, A*A, N] bool: the slab-test membership the render kernels of renderer r actually used (debug dump of the forward launch)."""
+    from nlos_gaussian_renderer_b200 import _lib
+    g = r.geom
+    N = params[0].shape[0]
+    dump = torch.zeros(g.n_tiles * 32, g.A * g.A, N, dtype=torch.uint8, device="cuda")
+    r.prepare(*params)
+    _lib.call("nlosb200_debug_hit_dump", dump.data_ptr())
+    try:
+        r.forward_tiled()
+        torch.cuda.synchronize()
+    finally:
+        _lib.call("nlosb200_debug_hit_dump", None)
+    out = torch.zeros(g.S, g.A * g.A, N, dtype=torch.uint8, device="cuda")
+    out[g.perm[g.valid]] = dump[g.valid]
+    return out.cpu().numpy().astype(bool)

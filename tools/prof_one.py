@@ -17,6 +17,10 @@ for a in sys.argv[4:]:
     k, v = a.split("=")
     if k == "rows":                       # rows=16: render only the first 16 scan rows of the grid (a slab, as one GPU of a sharded run would)
         rows = int(v)
+    elif k == "variant":                  # variant=wide|narrow|auto
+        kw[k] = v
+    elif k == "narrow_rays":
+        kw[k] = float(v)
     else:
         kw[k] = int(v)
 N, Sy, Sx, T, A = scenes.CONFIGS[cfg]
@@ -36,4 +40,4 @@ for _ in range(reps):
     g = r.backward_tiled(torch.ones_like(H))
     ev[2].record()
     torch.cuda.synchronize()
-    print(f"{cfg} {mode} {kw}: fwd {ev[0].elapsed_time(ev[1]):.2f} ms  bwd {ev[1].elapsed_time(ev[2]):.2f} ms  slice {r._slice} list {r.last_total}")
+    print(f"{cfg} {mode} {kw}: fwd {ev[0].elapsed_time(ev[1]):.2f} ms  bwd {ev[1].elapsed_time(ev[2]):.2f} ms  slice {r._slice} list {r.check_lists()}")
