@@ -113,6 +113,15 @@ class ScanGeometry:
                             self.phi_range[sl].reshape(n, self.Sx, 2), self.A, vp_y=self.vp_y, tile=(self.tile_y, self.tile_x),
                             device=self.device)
 
+    def select_rows(self, rows):
+        """Sub-geometry of the given scan rows (any subset, kept in the given order) -- what one GPU of a row-interleaved sharded run
+        renders (parallel.rank_rows)."""
+        idx = torch.as_tensor(list(rows), dtype=torch.long, device=self.scan_o.device)
+        n = int(idx.numel())
+        pick = lambda x, k: x.reshape(self.Sy, self.Sx, k)[idx]
+        return ScanGeometry(pick(self.scan_o, 3), pick(self.theta_range, 2), pick(self.phi_range, 2), self.A, vp_y=self.vp_y,
+                            tile=(self.tile_y, self.tile_x), device=self.device) if n else None
+
     # -- packing ---------------------------------------------------------------------------------
     def gather_tile_major(self, x):
         """[S,...] -> [n_tiles*32,...] in tile-major order (padding lanes repeat index 0)."""

@@ -16,6 +16,21 @@ def slab_rows(Sy, tile_y, rank, world):
     return min(t0 * tile_y, Sy), min(t1 * tile_y, Sy)
 
 
+def rank_rows(Sy, tile_y, rank, world, interleave=True):
+    """Scan rows of `rank` as a sorted index list.  interleave=True: tile rows (blocks of tile_y scan rows) are dealt round-robin,
+    tile row j -> rank j mod world, so that every rank gets near and far rows of the relay wall alike (the work per row varies with its
+    distance to the hidden volume: contiguous slabs left the 8-GPU step of BASELINE configs[3] waiting for the slowest slab);
+    interleave=False: the contiguous slab of slab_rows()."""
+    if not interleave:
+        y0, y1 = slab_rows(Sy, tile_y, rank, world)
+        return list(range(y0, y1))
+    n_tr = -(-Sy // tile_y)
+    rows = []
+    for j in range(rank, n_tr, world):
+        rows.extend(range(j * tile_y, min((j + 1) * tile_y, Sy)))
+    return rows
+
+
 def all_reduce_packed(dacc, group=None):
     """In-place sum of the packed gradient buffer over ranks (no-op for world size 1)."""
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
@@ -23,17 +38,21 @@ def all_reduce_packed(dacc, group=None):
     return dacc
 
 
-def gather_transient(H_slab, Sy, tile_y, group=None):
-    """All-gather the per-rank slabs [rows_r, Sx, T] into the full [Sy, Sx, T] transient (optional; fitting never needs it)."""
+def gather_transient(H_slab, Sy, tile_y, group=None, interleave=True):
+    """All-gather the per-rank row sets [rows_r, Sx, T] into the full [Sy, Sx, T] transient (optional; fitting never needs it).
+    `interleave` must be the partition the ranks rendered with (rank_rows)."""
     world = dist.get_world_size(group)
-    rank = dist.get_rank(group)
-    rows = [slab_rows(Sy, tile_y, r, world) for r in range(world)]
-    mx = max(b - a for a, b in rows)
+    rows = [rank_rows(Sy, tile_y, r, world, interleave) for r in range(world)]
+    mx = max(len(r) for r in rows)
     pad = torch.zeros(mx, *H_slab.shape[1:], dtype=H_slab.dtype, device=H_slab.device)
     pad[: H_slab.shape[0]] = H_slab
     outs = [torch.empty_like(pad) for _ in range(world)]
     dist.all_gather(outs, pad, group=group)
-    return torch.cat([o[: b - a] for o, (a, b) in zip(outs, rows)], 0)
+    full = torch.empty(Sy, *H_slab.shape[1:], dtype=H_slab.dtype, device=H_slab.device)
+    for o, r in zip(outs, rows):
+        if r:
+            full[torch.as_tensor(r, device=full.device)] = o[: len(r)]
+    return full
 
 
 class ShardedFitter:

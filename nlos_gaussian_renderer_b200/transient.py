@@ -33,13 +33,15 @@ class TransientRenderer:
     """Stateful renderer for one ScanGeometry: owns the preprocess / binning workspaces."""
 
     def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
-                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=2.5):
+                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=1.6):
         """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
         (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries a warp pulls at a time from its
         tile's counter (default: 16..256, sized so that every warp of the persistent grid gets >= 32 slices).
         variant: which scan-tile kernel renders an entry -- "wide" (register accumulators, transient.cu), "narrow" (direct to window,
         transient_narrow.cu) or "auto": per (tile, Gaussian) entry at binning time, narrow when the Gaussian's 3-sigma AABB spans at most
-        `narrow_rays` lattice pitches (the two kernels give the same result, they differ in speed only)."""
+        `narrow_rays` lattice pitches (the two kernels give the same result, they differ in speed only; measured crossover: BASELINE
+        configs[3], 1.8 hit rays per pair, is 16 % / 7 % faster forward / backward in the narrow kernel, configs[2], 3.5 hit rays, 7 % slower
+        forward)."""
         self.geom = geom
         self.T, self.t0, self.dt, self.c_deltaT = int(T), float(t0), float(dt), float(c_deltaT)
         self.mode = MODES[mode] if isinstance(mode, str) else int(mode)

@@ -42,4 +42,17 @@ def test_scene_table_holds_the_baseline_configurations():
     for k, v in want.items():
         assert tuple(scenes.CONFIGS[k][:4]) == v, k
     cfgs = json.load(open(os.path.join(ROOT, "BASELINE.json")))["configs"]
-    assert re.search(r"50k Gaussians, 64.64 confocal scan, 512 bins", cfgs[1])        # the bench default (configs[1])
+    assert re.search(r"50k Gaussians, 64.64 confocal scan, 512 bins", cfgs[1])
+    assert re.search(r"500k Gaussians to a synthetic 128.128.1024 transient", cfgs[3])   # the bench default (configs[3], the 1/2/4/8-GPU fitting loop)
+    import bench
+    sys.argv = ["bench.py"]
+    a = bench.parse()
+    assert a.config == "cfg4" and a.scaling == "strong" and a.gpus == 1 and a.mode == "analytic"
+
+
+def test_reference_arm_uses_every_core_under_torchrun_env():
+    """torchrun exports OMP_NUM_THREADS=1: the reference arm must ask for all host cores itself (round-1 SCALE ran it on one core at N >= 2)."""
+    p = _run({"OMP_NUM_THREADS": "1"})
+    assert p.returncode == 0, p.stderr[-2000:]
+    d = json.loads([ln for ln in p.stdout.splitlines() if ln.startswith("{")][0])
+    assert d["cpu_baseline"]["cores"] == (os.cpu_count() or 1)

@@ -60,9 +60,7 @@ def test_random_scene_forward_and_lists(seed):
         H8 = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mcut=8.0, **kw).forward(*params).cpu().numpy().reshape(Sy * Sx, T)
         assert util.rel_to_max(H8, H64) < TOL, case
     cnt, off, lst = r.lists()
-    klo, khi = oracle.shell_bins(util.np32(geom.scan_o), Sy, Sx, geom.tile_y, geom.tile_x, util.np32(params[0]), util.np32(params[1]),
-                                 1.0, 5.3, ta["t0"], ta["dt"], T, exp_mode=1)
-    ocnt, ooff, olst = oracle.window_lists(klo, khi, T, window, bucket)
+    (ocnt, ooff, olst), _ = util.oracle_window_lists(geom, ta, params, r)
     assert np.array_equal(cnt, ocnt) and np.array_equal(off, ooff) and np.array_equal(lst, olst)
 
 

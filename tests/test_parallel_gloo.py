@@ -28,6 +28,20 @@ def test_slab_rows_partition():
         assert max(tile_rows) - min(tile_rows) <= 1
 
 
+def test_rank_rows_partition_interleaved():
+    for Sy, ty, world in [(64, 4, 8), (66, 4, 4), (5, 4, 2), (128, 4, 3), (3, 4, 8), (128, 4, 8)]:
+        parts = [parallel.rank_rows(Sy, ty, r, world) for r in range(world)]
+        allr = sorted(sum(parts, []))
+        assert allr == list(range(Sy))                               # a partition
+        for r, rows in enumerate(parts):
+            assert all((y // ty) % world == r for y in rows)          # tile row j -> rank j mod world
+            assert rows == sorted(rows)
+        n_tr = [len({y // ty for y in rows}) for rows in parts]
+        assert max(n_tr) - min(n_tr) <= 1
+        assert [parallel.rank_rows(Sy, ty, r, world, interleave=False) for r in range(world)] == \
+            [list(range(*parallel.slab_rows(Sy, ty, r, world))) for r in range(world)]
+
+
 class _CpuStandIn:
     """forward/backward(reduce_fn) protocol of TransientRenderer on the CPU restatement (test infrastructure)."""
 
@@ -51,7 +65,7 @@ class _CpuStandIn:
         return packed
 
 
-def _worker(rank, world, port, Sy, out):
+def _worker(rank, world, port, Sy, out, interleave):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -59,27 +73,28 @@ def _worker(rank, world, port, Sy, out):
         ta = scenes.time_axis(24)
         params = scenes.make_gaussians(30, 5, scale_mul=3.0)
         target = torch.zeros(Sy, 3, 24, dtype=torch.float64)
-        y0, y1 = parallel.slab_rows(Sy, full.tile_y, rank, world)
-        slab = full.rows(y0, y1)
+        rows = parallel.rank_rows(Sy, full.tile_y, rank, world, interleave)
+        slab = full.select_rows(rows)
         _CpuStandIn.params0 = params
-        fit = parallel.ShardedFitter(_CpuStandIn(slab, ta), target[y0:y1], Sy * 3 * 24)
+        fit = parallel.ShardedFitter(_CpuStandIn(slab, ta), target[rows], Sy * 3 * 24)
         loss, packed = fit.step(*params)
         tot = loss.clone()
         dist.all_reduce(tot)
-        Hfull = parallel.gather_transient(fit.r.H.detach(), Sy, full.tile_y)
+        Hfull = parallel.gather_transient(fit.r.H.detach(), Sy, full.tile_y, interleave=interleave)
         if rank == 0:
             torch.save({"packed": packed, "loss": tot, "H": Hfull}, out)
     finally:
         dist.destroy_process_group()
 
 
-def test_two_rank_fit_step_equals_single_rank(tmp_path):
+@pytest.mark.parametrize("interleave", [True, False])
+def test_two_rank_fit_step_equals_single_rank(tmp_path, interleave):
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
-    Sy = 8
+    Sy = 16
     out = str(tmp_path / "r.pt")
-    mp.spawn(_worker, args=(2, port, Sy, out), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, port, Sy, out, interleave), nprocs=2, join=True)
     got = torch.load(out)
     # single process, full grid
     full = ScanGeometry.wall_grid(Sy, 3, A=4)
