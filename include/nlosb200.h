@@ -36,6 +36,11 @@ int nlosb200_preprocess_backward(const float* log_scales, const float* rotations
                                  int N, int sh_dim, float scaling_modifier, const float* dacc, float* d_means,
                                  float* d_log_scales, float* d_rotations, float* d_opacities, float* d_features, int accumulate,
                                  void* stream);
+/* the same with view-dependent albedo (sh_degree 1..3): d_features[:, :(sh_degree+1)^2] come from dsh [N,16] (nlosb200_transient_backward) */
+int nlosb200_preprocess_backward_sh(const float* log_scales, const float* rotations, const float* opacities, const float* features,
+                                    int N, int sh_dim, int sh_degree, float scaling_modifier, const float* dacc, const float* dsh, float* d_means,
+                                    float* d_log_scales, float* d_rotations, float* d_opacities, float* d_features, int accumulate,
+                                    void* stream);
 /* GaussianModel.get_bboxes (gaussian_model/gaussian_model.py:140-178) / bbox kernel: [N,6] min xyz, max xyz */
 int nlosb200_compute_bboxes(const float* means, const float* log_scales, const float* rotations, int N, float scaling_modifier,
                             float sigma, float* bboxes, void* stream);
@@ -76,15 +81,20 @@ int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float
  * walks class `cls` (nlosb200_bin_window_plan).  variant 0 = register-accumulator kernel (wide footprints, transient.cu), 1 = direct-to-window
  * kernel (footprints of a few rays, transient_narrow.cu); both render any entry, they differ in speed only.  accumulate = 0: H / dacc /
  * counters are zeroed by the callee first; 1: the launch adds to them (second class).  `work` is int32 scratch [n_tiles] (zeroed by the
- * callee): the per-tile slice counters the persistent CTAs pull work from; slice_len = list entries a warp takes at a time. */
+ * callee): the per-tile slice counters the persistent CTAs pull work from; slice_len = list entries a warp takes at a time.
+ * View-dependent albedo: sh_degree 1..3 with sh = the raw SH coefficients [N, sh_dim], sh_dim >= (sh_degree+1)^2 (fewer is an error: the
+ * reference reads out of bounds, volume_renderer.cu:110): albedo(g, p) = max(SH(dir(mu_g - o_p)) + 0.5, 0) per (Gaussian, scan point)
+ * (volume_renderer.cu:107-111, spherical_harmonics.cuh:20-80); the backward then also fills dsh [N,16] = dL/d(SH coefficients) and adds the
+ * direction's dependence on the mean to dL/dmu.  sh_degree 0: sh / dsh may be NULL, the degree-0 albedo of the record is used. */
 int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                               int mode, int variant, int accumulate, float* H, void* stream);
+                               int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H, void* stream);
 int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                 const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                 int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                                int mode, int variant, int accumulate, const float* grad_H, float* dacc, void* stream);
+                                int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree,
+                                const float* grad_H, float* dacc, float* dsh, void* stream);
 /* counters uint64 [4]: hit (g,ray) pairs, W_s, sample-evals evaluated, W_b */
 int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                              const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
@@ -109,6 +119,11 @@ int nlosb200_filter_gaussians_per_ray(const float* ray_origins, const float* ray
  * spherical_harmonics.cuh:20-80).  sh_dim < (degree+1)^2 is an error (the reference reads out of bounds). */
 int nlosb200_compat_albedo(const float* means, const float* features, const float* camera_pos, int N, int sh_dim,
                            int sh_degree, float* records, void* stream);
+/* backward of nlosb200_compat_albedo for active_sh_degree >= 1: dacc[g][13] = dL/d(albedo_g) (nlosb200_render_rays_backward) ->
+ * d_features [N, sh_dim] (overwritten) and d_means [N,3] += the dependence of the view direction on the mean.  Call after
+ * nlosb200_preprocess_backward. */
+int nlosb200_compat_albedo_backward(const float* means, const float* features, const float* camera_pos, int N, int sh_dim,
+                                    int sh_degree, const float* dacc, float* d_means, float* d_features, void* stream);
 /* _C.render_rays (include/volume_renderer.h:8-24, src/volume_renderer.cu:16-305) after nlosb200_preprocess (records, bboxes with
  * sigma 3.0 as volume_renderer.cu:232,244), nlosb200_compat_albedo and nlosb200_filter_gaussians_per_ray:
  * rho_density, density, transmittance each [n_rays, T]. */

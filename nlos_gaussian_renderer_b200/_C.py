@@ -5,7 +5,8 @@ implemented by libnlosb200.so through the C ABI (include/nlosb200.h).  torch onl
 
 Differences from the reference, all documented in DESIGN.md:
   * no cudaDeviceSynchronize, launches go to torch's current stream;
-  * active_sh_degree > 0 with too few feature columns raises instead of reading out of bounds;
+  * active_sh_degree > 0 with too few feature columns evaluates the highest degree the columns support, with ONE warning (the reference
+    reads out of bounds there; its own caller passes the dc column only, cuda_autograd.py:280);
   * `max_per_ray` / `max_sections` keyword extras (defaults = the reference's 256 / 128).
 """
 import torch
@@ -16,17 +17,40 @@ MAX_GAUSSIANS_PER_RAY = 256     # src/ray_aabb.cu:6
 MAX_SECTIONS_PER_RAY = 128      # src/volume_renderer_analytic.cu:11
 
 
-def _check(t, name):
-    """CHECK_INPUT of include/cuda_utils.cuh:7-9."""
+def _check(t, name, dtype=torch.float32):
+    """CHECK_INPUT of include/cuda_utils.cuh:7-9 + the dtype test data_ptr<float>() / data_ptr<int>() performs in the reference."""
     if not isinstance(t, torch.Tensor):
         raise TypeError(f"{name} must be a torch.Tensor")
     if not t.is_cuda:
         raise RuntimeError(f"{name} must be a CUDA tensor")
     if not t.is_contiguous():
         raise RuntimeError(f"{name} must be contiguous")
-    if t.dtype != torch.float32 and t.dtype != torch.int32:
-        raise RuntimeError(f"expected scalar type Float but found {t.dtype} ({name})")
+    if t.dtype != dtype:
+        raise RuntimeError(f"expected scalar type {'Float' if dtype == torch.float32 else 'Int'} but found {t.dtype} ({name})")
     return t
+
+
+_warned_sh = False
+
+
+def effective_sh_degree(active_sh_degree, n_coeffs):
+    """The reference's own caller passes ONLY the dc coefficient (cuda_autograd.py:280) while main.py:240-241 raises active_sh_degree almost
+    every iteration, so its kernel reads past the feature row (volume_renderer.cu:110, spherical_harmonics.cuh:72-77).  Documented choice here:
+    evaluate the highest degree the passed coefficients support (degree 0 for a dc-only row) and say so once."""
+    global _warned_sh
+    deg = int(active_sh_degree)
+    sup = 0
+    while sup < 3 and (sup + 2) ** 2 <= n_coeffs:
+        sup += 1
+    if deg > sup:
+        if not _warned_sh:
+            import warnings
+            warnings.warn(f"active_sh_degree={deg} but the features hold {n_coeffs} SH coefficient(s) per Gaussian: evaluating degree {sup} "
+                          "(the reference reads out of bounds here, volume_renderer.cu:110); pass get_features ([N,(deg+1)^2]) for view-dependent albedo",
+                          RuntimeWarning, stacklevel=3)
+            _warned_sh = True
+        return sup
+    return max(deg, 0)
 
 
 def _aligned(numel, dtype, device, align=128):
@@ -56,7 +80,7 @@ def filter_gaussians_per_ray(ray_origins, ray_directions, gaussian_means, gaussi
 
 class _Prepared:
     """records / bboxes / filter lists of one render_rays call (kept by the autograd function for the backward)."""
-    __slots__ = ("records", "bboxes", "filter", "cap", "N", "sh_dim")
+    __slots__ = ("records", "bboxes", "filter", "cap", "N", "sh_dim", "sh_degree", "camera_pos", "means")
 
 
 def _prepare(ray_origins, ray_directions, means, scales, rotations, opacities, features, camera_pos, sh_degree, scaling_modifier, cap):
@@ -67,6 +91,7 @@ def _prepare(ray_origins, ray_directions, means, scales, rotations, opacities, f
     P.N, P.cap = N, cap
     feats = features.reshape(N, -1) if N else features.reshape(0, 1)
     P.sh_dim = feats.shape[1]
+    sh_degree = P.sh_degree = effective_sh_degree(sh_degree, P.sh_dim)
     P.records = _aligned(max(N, 1) * L.nlosb200_record_floats(), torch.float32, dev, 128)
     P.bboxes = _aligned(max(N, 1) * 6, torch.float32, dev, 16)
     st = _lib.stream()
@@ -76,6 +101,7 @@ def _prepare(ray_origins, ray_directions, means, scales, rotations, opacities, f
                   N, P.sh_dim, float(scaling_modifier), 3.0, 0.0, P.records.data_ptr(), None, P.bboxes.data_ptr(), st)
         _lib.call("nlosb200_compat_albedo", means.data_ptr(), feats.data_ptr(), camera_pos.data_ptr(), N, P.sh_dim, int(sh_degree),
                   P.records.data_ptr(), st)
+    P.camera_pos, P.means = camera_pos, means
     n_rays = ray_origins.shape[0]
     P.filter = torch.empty(n_rays, cap + 1, dtype=torch.int32, device=dev)
     _lib.call("nlosb200_filter_gaussians_per_ray", ray_origins.data_ptr(), ray_directions.data_ptr(), P.bboxes.data_ptr(), n_rays, N, cap,
@@ -111,7 +137,8 @@ def render_rays_backward(P, ray_origins, ray_directions, t_samples, gaussian_sca
                          gaussian_features, c, deltaT, scaling_modifier, use_occlusion, rho_density, transmittance, grad_rho, grad_density,
                          grad_transmittance):
     """Gradients of (rho_density, density, transmittance) w.r.t. (means, scales, rotations, opacities, features)
-    -- the kernel call commented out in gaussian_model/cuda_autograd.py:139-172.  Degree-0 albedo chain."""
+    -- the kernel call commented out in gaussian_model/cuda_autograd.py:139-172.  active_sh_degree >= 1: the albedo's dependence on the SH
+    coefficients and on the mean (through the view direction) is chained by nlosb200_compat_albedo_backward."""
     N, dev = P.N, ray_origins.device
     n_rays, T = ray_origins.shape[0], t_samples.shape[0]
     L = _lib.lib()
@@ -131,6 +158,9 @@ def render_rays_backward(P, ray_origins, ray_directions, t_samples, gaussian_sca
     if N:
         _lib.call("nlosb200_preprocess_backward", gaussian_scales.data_ptr(), gaussian_rotations.data_ptr(), opac.data_ptr(),
                   feats.data_ptr(), N, feats.shape[1], float(scaling_modifier), dacc.data_ptr(), *[o.data_ptr() for o in outs], 0, st)
+        if P.sh_degree > 0:
+            _lib.call("nlosb200_compat_albedo_backward", P.means.data_ptr(), feats.data_ptr(), P.camera_pos.data_ptr(), N, feats.shape[1],
+                      P.sh_degree, dacc.data_ptr(), outs[0].data_ptr(), outs[4].data_ptr(), st)
     return outs[0], outs[1], outs[2], outs[3].reshape(gaussian_opacities.shape), outs[4].reshape(gaussian_features.shape)
 
 
@@ -140,11 +170,11 @@ def render_rays_analytic(ray_origins, ray_directions, t_min, t_max, gaussian_fil
     """-> [N_rays] (src/volume_renderer_analytic.cu:178-241).  c, deltaT and rendering_type are accepted and unused,
     like the reference kernel."""
     _check(ray_origins, "ray_origins"); _check(ray_directions, "ray_directions"); _check(gaussian_means, "gaussian_means")
-    for t, n in ((gaussian_filter, "gaussian_filter"), (gaussian_scales, "gaussian_scales"), (gaussian_rotations, "gaussian_rotations"),
+    _check(gaussian_filter, "gaussian_filter", torch.int32)
+    for t, n in ((gaussian_scales, "gaussian_scales"), (gaussian_rotations, "gaussian_rotations"),
                  (gaussian_opacities, "gaussian_opacities"), (gaussian_features, "gaussian_features"), (camera_pos, "camera_pos")):
         _check(t, n)
-    if gaussian_filter.dtype != torch.int32:
-        raise RuntimeError("expected scalar type Int for gaussian_filter")
+
     n_rays, N = ray_origins.shape[0], gaussian_means.shape[0]
     cap = gaussian_filter.shape[1] - 1
     ms = MAX_SECTIONS_PER_RAY if max_sections is None else int(max_sections)
@@ -152,7 +182,8 @@ def render_rays_analytic(ray_origins, ray_directions, t_min, t_max, gaussian_fil
     out = torch.zeros(n_rays, dtype=torch.float32, device=ray_origins.device)
     _lib.call("nlosb200_render_rays_analytic", ray_origins.data_ptr(), ray_directions.data_ptr(), float(t_min), float(t_max),
               gaussian_filter.data_ptr(), cap, gaussian_means.data_ptr(), gaussian_scales.data_ptr(), gaussian_rotations.data_ptr(),
-              gaussian_opacities.data_ptr(), feats.data_ptr(), camera_pos.data_ptr(), n_rays, N, feats.shape[1], int(active_sh_degree),
+              gaussian_opacities.data_ptr(), feats.data_ptr(), camera_pos.data_ptr(), n_rays, N, feats.shape[1],
+              effective_sh_degree(active_sh_degree, feats.shape[1]),
               float(scaling_modifier), float(sigma_threshold), ms, out.data_ptr(), _lib.stream())
     return out
 
@@ -178,7 +209,7 @@ def evaluate_points(points, gaussian_means, gaussian_scales, gaussian_rotations,
         if camera_pos is not None:
             _check(camera_pos, "camera_pos")
             _lib.call("nlosb200_compat_albedo", gaussian_means.data_ptr(), feats.data_ptr(), camera_pos.data_ptr(), N, feats.shape[1],
-                      int(active_sh_degree), records.data_ptr(), st)
+                      effective_sh_degree(active_sh_degree, feats.shape[1]), records.data_ptr(), st)
     Na = points.shape[0]
     density = torch.zeros(Na, dtype=torch.float32, device=dev)
     rho_density = torch.zeros(Na, dtype=torch.float32, device=dev)

@@ -130,6 +130,79 @@ __device__ __forceinline__ bool ray_aabb_x(float ox, float oy, float oz, float d
     return tmax >= tmin && tmax >= 0.0f;
 }
 
+// ---------------------------------------------------------------- spherical harmonics (degree 0..3)
+// include/spherical_harmonics.cuh:20-80 of the reference: real SH as polynomials of the (normalised) view direction, ALL-POSITIVE sign
+// convention (not the PlenOctree signs of gaussian_model/sh_utils.py), coefficient order l = 0..degree, m = -l..l.
+__device__ __forceinline__ void sh_basis_all(int degree, float x, float y, float z, float* Y)
+{
+    Y[0] = 0.28209479177387814f;
+    if (degree >= 1) {
+        Y[1] = 0.4886025119029199f * y; Y[2] = 0.4886025119029199f * z; Y[3] = 0.4886025119029199f * x;
+    }
+    if (degree >= 2) {
+        Y[4] = 1.0925484305920792f * x * y; Y[5] = 1.0925484305920792f * y * z;
+        Y[6] = 0.31539156525252005f * (3.0f * z * z - 1.0f);
+        Y[7] = 1.0925484305920792f * x * z; Y[8] = 0.5462742152960396f * (x * x - y * y);
+    }
+    if (degree >= 3) {
+        Y[9] = 0.5900435899266435f * y * (3.0f * x * x - y * y); Y[10] = 2.890611442640554f * x * y * z;
+        Y[11] = 0.4570457994644658f * y * (5.0f * z * z - 1.0f); Y[12] = 0.3731763325901154f * z * (5.0f * z * z - 3.0f);
+        Y[13] = 0.4570457994644658f * x * (5.0f * z * z - 1.0f); Y[14] = 1.445305721320277f * z * (x * x - y * y);
+        Y[15] = 0.5900435899266435f * x * (x * x - 3.0f * y * y);
+    }
+}
+// gradient of  sum_k f[k] Y_k(x, y, z)  with respect to (x, y, z), the polynomials taken as functions of three free variables
+__device__ __forceinline__ void sh_grad_all(int degree, const float* f, float x, float y, float z, float& gx, float& gy, float& gz)
+{
+    gx = gy = gz = 0.f;
+    if (degree >= 1) {
+        gy += 0.4886025119029199f * f[1]; gz += 0.4886025119029199f * f[2]; gx += 0.4886025119029199f * f[3];
+    }
+    if (degree >= 2) {
+        const float a = 1.0925484305920792f, b = 0.31539156525252005f, c = 0.5462742152960396f;
+        gx += a * (f[4] * y + f[7] * z) + 2.0f * c * f[8] * x;
+        gy += a * (f[4] * x + f[5] * z) - 2.0f * c * f[8] * y;
+        gz += a * (f[5] * y + f[7] * x) + 6.0f * b * f[6] * z;
+    }
+    if (degree >= 3) {
+        const float a = 0.5900435899266435f, b = 2.890611442640554f, c = 0.4570457994644658f, d = 0.3731763325901154f, e = 1.445305721320277f;
+        const float zz = 5.0f * z * z - 1.0f;
+        gx += a * f[9] * 6.0f * x * y + b * f[10] * y * z + c * f[13] * zz + e * f[14] * 2.0f * x * z + a * f[15] * 3.0f * (x * x - y * y);
+        gy += a * f[9] * 3.0f * (x * x - y * y) + b * f[10] * x * z + c * f[11] * zz - e * f[14] * 2.0f * y * z - a * f[15] * 6.0f * x * y;
+        gz += b * f[10] * x * y + c * f[11] * 10.0f * y * z + d * f[12] * (15.0f * z * z - 3.0f) + c * f[13] * 10.0f * x * z + e * f[14] * (x * x - y * y);
+    }
+}
+// albedo of one (Gaussian, scan point) pair:  max(SH(dir(mu - o)) + 0.5, 0)  with dir = c / (|c| + 1e-8)  (volume_renderer.cu:107-111,
+// cuda_utils.cuh:48-51).  c = mu - o, D = |c|.  Kept out of line: only scenes with active_sh_degree > 0 pay for it.
+static __device__ __noinline__ float sh_pair_albedo(const float* __restrict__ f, int degree, float cx, float cy, float cz, float D)
+{
+    const float s = 1.0f / (D + 1e-8f);
+    float Y[16];
+    sh_basis_all(degree, cx * s, cy * s, cz * s, Y);
+    const int K = (degree + 1) * (degree + 1);
+    float r = 0.f;
+    for (int i = 0; i < K; ++i) r = fmaf(__ldg(f + i), Y[i], r);
+    return fmaxf(r + 0.5f, 0.0f);
+}
+// backward of the above for one pair: dpre = dL/d(SH value) (0 where the clamp is active).  Writes dsh[k] = dpre Y_k and ADDS dL/dmu to (gmx, gmy, gmz):
+// d dir = s dc - dir (dir . dc) / D  with s = 1 / (D + 1e-8).
+static __device__ __noinline__ void sh_pair_backward(const float* __restrict__ f, int degree, float cx, float cy, float cz, float D, float dpre,
+                                              float* dsh, float& gmx, float& gmy, float& gmz)
+{
+    const float s = 1.0f / (D + 1e-8f);
+    const float x = cx * s, y = cy * s, z = cz * s;
+    float Y[16], fl[16];
+    sh_basis_all(degree, x, y, z, Y);
+    const int K = (degree + 1) * (degree + 1);
+    for (int i = 0; i < 16; ++i) { fl[i] = i < K ? __ldg(f + i) : 0.f; dsh[i] = i < K ? dpre * Y[i] : 0.f; }
+    float gx, gy, gz;
+    sh_grad_all(degree, fl, x, y, z, gx, gy, gz);
+    const float vd = (x * gx + y * gy + z * gz) / fmaxf(D, 1e-30f);
+    gmx = fmaf(dpre, s * gx - x * vd, gmx);
+    gmy = fmaf(dpre, s * gy - y * vd, gmy);
+    gmz = fmaf(dpre, s * gz - z * vd, gmz);
+}
+
 // ---------------------------------------------------------------- fast math (SFU aware)
 __device__ __forceinline__ float ex2_approx(float x)
 {

@@ -120,25 +120,6 @@ extern "C" int nlosb200_filter_gaussians_per_ray(const float* ray_origins, const
 // (volume_renderer.cu:107-111, spherical_harmonics.cuh:20-80 -- the all-positive sign convention of the
 // CUDA reference, NOT the PlenOctree signs of gaussian_model/sh_utils.py).  Writes REC_ALB of each record.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void sh_basis_all(int degree, float x, float y, float z, float* Y)
-{
-    Y[0] = 0.28209479177387814f;
-    if (degree >= 1) {
-        Y[1] = 0.4886025119029199f * y; Y[2] = 0.4886025119029199f * z; Y[3] = 0.4886025119029199f * x;
-    }
-    if (degree >= 2) {
-        Y[4] = 1.0925484305920792f * x * y; Y[5] = 1.0925484305920792f * y * z;
-        Y[6] = 0.31539156525252005f * (3.0f * z * z - 1.0f);
-        Y[7] = 1.0925484305920792f * x * z; Y[8] = 0.5462742152960396f * (x * x - y * y);
-    }
-    if (degree >= 3) {
-        Y[9] = 0.5900435899266435f * y * (3.0f * x * x - y * y); Y[10] = 2.890611442640554f * x * y * z;
-        Y[11] = 0.4570457994644658f * y * (5.0f * z * z - 1.0f); Y[12] = 0.3731763325901154f * z * (5.0f * z * z - 3.0f);
-        Y[13] = 0.4570457994644658f * x * (5.0f * z * z - 1.0f); Y[14] = 1.445305721320277f * z * (x * x - y * y);
-        Y[15] = 0.5900435899266435f * x * (x * x - 3.0f * y * y);
-    }
-}
-
 __global__ void __launch_bounds__(256) compat_albedo_kernel(const float* __restrict__ means, const float* __restrict__ feats,
                                                             const float* __restrict__ cam, int N, int sh_dim, int degree,
                                                             float* __restrict__ records)
@@ -154,6 +135,27 @@ __global__ void __launch_bounds__(256) compat_albedo_kernel(const float* __restr
     float r = 0.f;
     for (int i = 0; i < K; ++i) r = fmaf(feats[(size_t)g * sh_dim + i], Y[i], r);
     records[(size_t)g * NLOS_REC_FLOATS + REC_ALB] = fmaxf(r + 0.5f, 0.0f);
+}
+
+// backward of compat_albedo_kernel (the reference has none): dalb = dacc[g][13] = dL/d(albedo_g) -> d_features[g, :] (overwritten) and
+// d_means[g] += the dependence of the view direction on the mean
+__global__ void __launch_bounds__(256) compat_albedo_backward_kernel(const float* __restrict__ means, const float* __restrict__ feats,
+                                                                     const float* __restrict__ cam, int N, int sh_dim, int degree,
+                                                                     const float* __restrict__ dacc, float* __restrict__ d_means,
+                                                                     float* __restrict__ d_feats)
+{
+    int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= N) return;
+    const float cx = means[3 * g + 0] - cam[0], cy = means[3 * g + 1] - cam[1], cz = means[3 * g + 2] - cam[2];
+    const float D = sqrtf(cx * cx + cy * cy + cz * cz);
+    const float* f = feats + (size_t)g * sh_dim;
+    const float alb = sh_pair_albedo(f, degree, cx, cy, cz, D);
+    const float dpre = alb > 0.f ? dacc[(size_t)g * NLOS_GRAD_FLOATS + 13] : 0.f;
+    float dsh[16], gx = 0.f, gy = 0.f, gz = 0.f;
+    sh_pair_backward(f, degree, cx, cy, cz, D, dpre, dsh, gx, gy, gz);
+    const int K = (degree + 1) * (degree + 1);
+    for (int k = 0; k < sh_dim; ++k) d_feats[(size_t)g * sh_dim + k] = k < K ? dsh[k] : 0.f;
+    d_means[3 * g + 0] += gx; d_means[3 * g + 1] += gy; d_means[3 * g + 2] += gz;
 }
 
 // per-(Gaussian, ray) set-up shared by the forward and backward kernels: centred quadratic of
@@ -555,6 +557,20 @@ extern "C" int nlosb200_compat_albedo(const float* means, const float* features,
     NLOS_REQUIRE(means && features && camera_pos && records, "compat_albedo: null pointer");
     compat_albedo_kernel<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(means, features, camera_pos, N, sh_dim, sh_degree, records);
     NLOS_CHECK_LAUNCH("compat_albedo_kernel");
+    return 0;
+}
+
+extern "C" int nlosb200_compat_albedo_backward(const float* means, const float* features, const float* camera_pos, int N, int sh_dim,
+                                               int sh_degree, const float* dacc, float* d_means, float* d_features, void* stream)
+{
+    if (N <= 0) return 0;
+    NLOS_REQUIRE(sh_degree >= 0 && sh_degree <= 3, "compat_albedo_backward: active_sh_degree=%d not in [0,3]", sh_degree);
+    NLOS_REQUIRE(sh_dim >= (sh_degree + 1) * (sh_degree + 1), "compat_albedo_backward: %d SH coefficients, degree %d needs %d", sh_dim, sh_degree,
+                 (sh_degree + 1) * (sh_degree + 1));
+    NLOS_REQUIRE(means && features && camera_pos && dacc && d_means && d_features, "compat_albedo_backward: null pointer");
+    compat_albedo_backward_kernel<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(means, features, camera_pos, N, sh_dim, sh_degree, dacc, d_means,
+                                                                                   d_features);
+    NLOS_CHECK_LAUNCH("compat_albedo_backward_kernel");
     return 0;
 }
 

@@ -98,7 +98,8 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const float* _
                                                                   int sh_dim, float mod, const float* __restrict__ dacc,
                                                                   float* __restrict__ d_means, float* __restrict__ d_scales,
                                                                   float* __restrict__ d_rots, float* __restrict__ d_opac,
-                                                                  float* __restrict__ d_feats, int accumulate)
+                                                                  float* __restrict__ d_feats, int accumulate, const float* __restrict__ dsh = nullptr,
+                                                                  int sh_degree = 0)
 {
     int g = blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= N) return;
@@ -149,6 +150,17 @@ __global__ void __launch_bounds__(256) preprocess_backward_kernel(const float* _
     float dopac = dop * op * (1.0f - op);
     float f0 = feats[(size_t)g * sh_dim];
     float df0 = (fmaf(NLOS_SH_C0, f0, 0.5f) > 0.f) ? dalb * NLOS_SH_C0 : 0.f;
+    if (sh_degree > 0) {            // view-dependent albedo: the render backward already reduced dL/d(SH coefficients) over the scan points
+        const int K = (sh_degree + 1) * (sh_degree + 1);
+        for (int i = 0; i < 3; ++i) { d_means[3 * g + i] = (accumulate ? d_means[3 * g + i] : 0.f) + dmu[i]; d_scales[3 * g + i] = (accumulate ? d_scales[3 * g + i] : 0.f) + dls[i]; }
+        for (int i = 0; i < 4; ++i) d_rots[4 * g + i] = (accumulate ? d_rots[4 * g + i] : 0.f) + dq[i];
+        d_opac[g] = (accumulate ? d_opac[g] : 0.f) + dopac;
+        for (int k = 0; k < sh_dim; ++k) {
+            float v = k < K ? dsh[(size_t)g * 16 + k] : 0.f;
+            d_feats[(size_t)g * sh_dim + k] = (accumulate ? d_feats[(size_t)g * sh_dim + k] : 0.f) + v;
+        }
+        return;
+    }
     if (accumulate) {
         for (int i = 0; i < 3; ++i) { d_means[3 * g + i] += dmu[i]; d_scales[3 * g + i] += dls[i]; }
         for (int i = 0; i < 4; ++i) d_rots[4 * g + i] += dq[i];
@@ -175,6 +187,23 @@ extern "C" int nlosb200_preprocess_backward(const float* log_scales, const float
                                                                                   scaling_modifier, dacc, d_means, d_log_scales, d_rotations,
                                                                                   d_opacities, d_features, accumulate);
     NLOS_CHECK_LAUNCH("preprocess_backward_kernel");
+    return 0;
+}
+
+extern "C" int nlosb200_preprocess_backward_sh(const float* log_scales, const float* rotations, const float* opacities, const float* features,
+                                               int N, int sh_dim, int sh_degree, float scaling_modifier, const float* dacc, const float* dsh,
+                                               float* d_means, float* d_log_scales, float* d_rotations, float* d_opacities, float* d_features,
+                                               int accumulate, void* stream)
+{
+    if (N <= 0) return 0;
+    NLOS_REQUIRE(dacc && d_means && d_log_scales && d_rotations && d_opacities && d_features, "preprocess_backward_sh: null pointer");
+    NLOS_REQUIRE(sh_degree >= 0 && sh_degree <= 3 && (sh_degree == 0 || (dsh && sh_dim >= (sh_degree + 1) * (sh_degree + 1))),
+                 "preprocess_backward_sh: degree %d with %d coefficients / null dsh", sh_degree, sh_dim);
+    NLOS_REQUIRE(((uintptr_t)dacc % 16) == 0, "preprocess_backward_sh: dacc must be 16-byte aligned");
+    preprocess_backward_kernel<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(log_scales, rotations, opacities, features, N, sh_dim,
+                                                                                  scaling_modifier, dacc, d_means, d_log_scales, d_rotations,
+                                                                                  d_opacities, d_features, accumulate, dsh, sh_degree);
+    NLOS_CHECK_LAUNCH("preprocess_backward_kernel(sh)");
     return 0;
 }
 

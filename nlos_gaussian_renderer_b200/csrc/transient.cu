@@ -211,7 +211,6 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                     const float4* rec = reinterpret_cast<const float4*>(ring + ((rb & 1u) * TR_RING + q) * NLOS_REC_FLOATS);
                     const float4 v0 = rec[0], v1 = rec[1], v2 = rec[2], v3 = rec[3], v4 = rec[4], v5 = rec[5];
                     const float M00 = v1.x, M01 = v1.y, M02 = v1.z, M10 = v1.w, M11 = v2.x, M12 = v2.y, M20 = v2.z, M21 = v2.w, M22 = v3.x;
-                    const float opalb = v0.w * v4.w;
                     const float cx = v0.x - ox, cy = v0.y - oy, cz = v0.z - oz;                             // mu - o
                     // ---- the tile-level shell [klo, khi] of this Gaussian comes with the list entry (binning.cu:shell_bins)
                     int s_lo, s_hi;
@@ -240,13 +239,13 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                     float gwa = 0.f;                                                                        // dL/d(op*alb)
                     // numerical backward: the same sums with ray 0 / ray 1 of an iteration in the two halves of packed registers
                     f32x2 pga[3] = {0ull, 0ull, 0ull}, pg[9] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull}, pgwa = 0ull;
-                    bool act = valid && (MODE == MODE_COUNT || opalb > 0.f);
-                    float D = 0.f;
-                    if (act) {
-                        // radial reject of this scan point against the entry's bins
-                        D = sqrtf(d2);
-                        act = (D + v5.x >= r_in) && (D - v5.x <= r_out);
-                    }
+                    const float D = sqrtf(d2);
+                    float alb = v4.w;                                                                       // degree-0 albedo of the record
+                    if (MODE != MODE_COUNT && P.sh_degree > 0)                                              // view-dependent: one albedo per (Gaussian, scan point)
+                        alb = sh_pair_albedo(P.sh + (size_t)(ent & ((1u << NLOS_ENTRY_SHIFT) - 1u)) * P.sh_dim, P.sh_degree, cx, cy, cz, D);
+                    const float opalb = v0.w * alb;
+                    // radial reject of this scan point against the entry's bins
+                    const bool act = valid && (MODE == MODE_COUNT || opalb > 0.f) && (D + v5.x >= r_in) && (D - v5.x <= r_out);
                     if (act) {
                         const float lox = v3.y - ox, loy = v3.z - oy, loz = v3.w - oz;                      // AABB relative to the scan point
                         const float hix = v4.x - ox, hiy = v4.y - oy, hiz = v4.z - oz;
@@ -790,37 +789,31 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                             gwa += lo_of(pgwa) + hi_of(pgwa);
                         }
                         // a = M (o - mu) = -M c :  dL/dM += dL/da (x) (o - mu) ;  dL/dmu = -M^T dL/da
-                        float o[13];
-                        o[0] = fmaf(-gax, cx, g00); o[1] = fmaf(-gax, cy, g01); o[2] = fmaf(-gax, cz, g02);
-                        o[3] = fmaf(-gay, cx, g10); o[4] = fmaf(-gay, cy, g11); o[5] = fmaf(-gay, cz, g12);
-                        o[6] = fmaf(-gaz, cx, g20); o[7] = fmaf(-gaz, cy, g21); o[8] = fmaf(-gaz, cz, g22);
-                        o[9] = -(M00 * gax + M10 * gay + M20 * gaz);
-                        o[10] = -(M01 * gax + M11 * gay + M21 * gaz);
-                        o[11] = -(M02 * gax + M12 * gay + M22 * gaz);
-                        o[12] = gwa;
-                        // transposing butterfly: 16 shuffles reduce the 13 sums over the warp (instead of 13 x 5); after the step with
-                        // lane-xor 16/8/4/2 each lane keeps half of its slots, so slot index = lane bits 4..1 and lanes 2i, 2i+1 both end
-                        // with the total of slot i
                         float v[16];
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = i < 13 ? o[i] : 0.f;
-#pragma unroll
-                        for (int half = 8, bit = 16; half >= 1; half >>= 1, bit >>= 1) {
-                            const bool up = lane & bit;
-#pragma unroll
-                            for (int i = 0; i < half; ++i) {
-                                const float send = up ? v[i] : v[i + half], keep = up ? v[i + half] : v[i];
-                                v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
-                            }
-                        }
-                        float val = v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
-                        const int slot = lane >> 1;
+                        v[0] = fmaf(-gax, cx, g00); v[1] = fmaf(-gax, cy, g01); v[2] = fmaf(-gax, cz, g02);
+                        v[3] = fmaf(-gay, cx, g10); v[4] = fmaf(-gay, cy, g11); v[5] = fmaf(-gay, cz, g12);
+                        v[6] = fmaf(-gaz, cx, g20); v[7] = fmaf(-gaz, cy, g21); v[8] = fmaf(-gaz, cz, g22);
+                        v[9] = -(M00 * gax + M10 * gay + M20 * gaz);
+                        v[10] = -(M01 * gax + M11 * gay + M21 * gaz);
+                        v[11] = -(M02 * gax + M12 * gay + M22 * gaz);
+                        v[12] = gwa * alb;                                       // dL/dop      (gwa = dL/d(op * albedo) of this pair)
+                        v[13] = gwa * v0.w;                                      // dL/dalbedo  (degree 0: one albedo per Gaussian)
+                        v[14] = 0.f; v[15] = 0.f;
                         const int g = (int)(ent & ((1u << NLOS_ENTRY_SHIFT) - 1u));
-                        // slots: 0..8 dM, 9..11 dmu, 12 dop = alb * d(op*alb), 13 dalb = op * d(op*alb) (the two lanes of slot 12 write these)
-                        int dst = slot;
-                        bool wr = !(lane & 1) && slot < 12;
-                        if (slot == 12) { val *= (lane & 1) ? v0.w : v4.w; dst = 12 + (lane & 1); wr = true; }
-                        if (wr && val != 0.f) atomicAdd(P.dacc + (size_t)g * NLOS_GRAD_FLOATS + dst, val);
+                        const int slot = lane >> 1;
+                        if (P.sh_degree > 0) {
+                            // view-dependent albedo: dL/d(SH coefficients) = sum over the scan points of dpre Y_k(dir), and the direction's own
+                            // dependence on the mean goes into dL/dmu (slots 9..11)
+                            float dshv[16];
+                            const float dpre = alb > 0.f ? v[13] : 0.f;
+                            v[13] = 0.f;
+                            sh_pair_backward(P.sh + (size_t)g * P.sh_dim, P.sh_degree, cx, cy, cz, D, dpre, dshv, v[9], v[10], v[11]);
+                            const float sval = warp_reduce16(dshv, lane);
+                            if (!(lane & 1) && sval != 0.f) atomicAdd(P.dsh + (size_t)g * 16 + slot, sval);
+                        }
+                        // slots: 0..8 dM, 9..11 dmu, 12 dop, 13 dalb (degree 0)
+                        const float val = warp_reduce16(v, lane);
+                        if (!(lane & 1) && slot < 14 && val != 0.f) atomicAdd(P.dacc + (size_t)g * NLOS_GRAD_FLOATS + slot, val);
                     }
                 }
                 __syncwarp();
@@ -872,8 +865,13 @@ extern "C" int nlosb200_debug_hit_dump(unsigned char* hits) { g_hit_dump = hits;
 
 static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                        const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls, int* work, float t0,
-                       float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, int variant)
+                       float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, int variant,
+                       const float* sh = nullptr, int sh_dim = 0, int sh_degree = 0)
 {
+    NLOS_REQUIRE(sh_degree >= 0 && sh_degree <= 3, "transient: active_sh_degree=%d not in [0,3]", sh_degree);
+    NLOS_REQUIRE(sh_degree == 0 || (sh && sh_dim >= (sh_degree + 1) * (sh_degree + 1)),
+                 "transient: degree %d needs %d SH coefficients per Gaussian, features hold %d (the reference reads out of bounds here, volume_renderer.cu:110)",
+                 sh_degree, (sh_degree + 1) * (sh_degree + 1), sh_dim);
     NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && A >= 1 && A <= 128, "transient: bad sizes");
     NLOS_REQUIRE(window >= 32 && window % 8 == 0 && bucket >= 1 && (bucket & (bucket - 1)) == 0 && 2 * bucket <= window && slice_len > 0,
                  "transient: bad window/bucket/slice_len (bucket must be a power of two)");
@@ -891,6 +889,7 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
     P.cpt = n_classes * P.n_buckets; P.cell0 = cls * P.n_buckets;
     P.slice_len = slice_len; P.flush_scale = mode == MODE_NUM ? c_deltaT : 1.0f; P.mcut2 = mcut * mcut;
     P.H = nullptr; P.gH = nullptr; P.dacc = nullptr; P.counters = nullptr; P.hit_dump = g_hit_dump;
+    P.sh = sh; P.sh_dim = sh_dim; P.sh_degree = sh_degree; P.dsh = nullptr;
     return 0;
 }
 
@@ -899,11 +898,11 @@ extern "C" int nlosb200_transient_warps_per_block(void) { return TR_WPB; }
 extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                           const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                           int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                                          int mode, int variant, int accumulate, float* H, void* stream)
+                                          int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H, void* stream)
 {
     TransientParams P;
     int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
-                         bucket, slice_len, c_deltaT, mcut, mode, variant);
+                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree);
     if (rc) return rc;
     NLOS_REQUIRE(H, "transient_forward: null H");
     cudaStream_t s = (cudaStream_t)stream;
@@ -920,20 +919,26 @@ extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A
 extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                            const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                            int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                                           int mode, int variant, int accumulate, const float* grad_H, float* dacc, void* stream)
+                                           int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree,
+                                           const float* grad_H, float* dacc, float* dsh, void* stream)
 {
     TransientParams P;
     int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
-                         bucket, slice_len, c_deltaT, mcut, mode, variant);
+                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree);
     if (rc) return rc;
-    NLOS_REQUIRE(grad_H && dacc, "transient_backward: null pointer");
+    NLOS_REQUIRE(grad_H && dacc && (sh_degree == 0 || dsh), "transient_backward: null pointer");
     cudaStream_t s = (cudaStream_t)stream;
     if (!accumulate) {
         cudaError_t e = cudaMemsetAsync(dacc, 0, (size_t)N * NLOS_GRAD_FLOATS * sizeof(float), s);
         NLOS_REQUIRE(e == cudaSuccess, "transient_backward: memset: %s", cudaGetErrorString(e));
+        if (sh_degree > 0) {
+            e = cudaMemsetAsync(dsh, 0, (size_t)N * 16 * sizeof(float), s);
+            NLOS_REQUIRE(e == cudaSuccess, "transient_backward: memset: %s", cudaGetErrorString(e));
+        }
     }
     P.gH = grad_H;
     P.dacc = dacc;
+    P.dsh = dsh;
     if (variant == 1) return launch_transient_narrow(P, mode, true, s);
     return mode == MODE_NUM ? launch_transient<MODE_NUM, true>(P, s, "transient_kernel<num,bwd>")
                             : launch_transient<MODE_ANA, true>(P, s, "transient_kernel<ana,bwd>");

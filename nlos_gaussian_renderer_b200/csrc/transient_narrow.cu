@@ -186,7 +186,6 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     const float4* rec = reinterpret_cast<const float4*>(ring + ((rb & 1u) * TR_RING + q) * NLOS_REC_FLOATS);
                     const float4 v0 = rec[0], v1 = rec[1], v2 = rec[2], v3 = rec[3], v4 = rec[4], v5 = rec[5], v6 = rec[6];
                     const float M00 = v1.x, M01 = v1.y, M02 = v1.z, M10 = v1.w, M11 = v2.x, M12 = v2.y, M20 = v2.z, M21 = v2.w, M22 = v3.x;
-                    const float opalb = v0.w * v4.w;
                     const float cx = v0.x - ox, cy = v0.y - oy, cz = v0.z - oz;                             // mu - o
                     // ---- the tile-level shell [klo, khi] of this Gaussian comes with the list entry (binning.cu:shell_bins)
                     int s_lo, s_hi;
@@ -217,6 +216,10 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     f32x2 pga[3] = {0ull, 0ull, 0ull}, pg[9] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull}, pgwa = 0ull;
                     // ---- the pair (this lane's scan point): radial reject against the entry's bins, AABB relative to the scan point, a = M (o - mu)
                     const float D = sqrtf(d2);
+                    float alb = v4.w;                                                                       // degree-0 albedo of the record
+                    if (P.sh_degree > 0)                                                                    // view-dependent: one albedo per (Gaussian, scan point)
+                        alb = sh_pair_albedo(P.sh + (size_t)(ent & ((1u << NLOS_ENTRY_SHIFT) - 1u)) * P.sh_dim, P.sh_degree, cx, cy, cz, D);
+                    const float opalb = v0.w * alb;
                     const bool act = valid && opalb > 0.f && (D + v5.x >= r_in) && (D - v5.x <= r_out);
                     const float lox = v3.y - ox, loy = v3.z - oy, loz = v3.w - oz;
                     const float hix = v4.x - ox, hiy = v4.y - oy, hiz = v4.z - oz;
@@ -771,37 +774,31 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                             gwa += lo_of(pgwa) + hi_of(pgwa);
                         }
                         // a = M (o - mu) = -M c :  dL/dM += dL/da (x) (o - mu) ;  dL/dmu = -M^T dL/da
-                        float o[13];
-                        o[0] = fmaf(-gax, cx, g00); o[1] = fmaf(-gax, cy, g01); o[2] = fmaf(-gax, cz, g02);
-                        o[3] = fmaf(-gay, cx, g10); o[4] = fmaf(-gay, cy, g11); o[5] = fmaf(-gay, cz, g12);
-                        o[6] = fmaf(-gaz, cx, g20); o[7] = fmaf(-gaz, cy, g21); o[8] = fmaf(-gaz, cz, g22);
-                        o[9] = -(M00 * gax + M10 * gay + M20 * gaz);
-                        o[10] = -(M01 * gax + M11 * gay + M21 * gaz);
-                        o[11] = -(M02 * gax + M12 * gay + M22 * gaz);
-                        o[12] = gwa;
-                        // transposing butterfly: 16 shuffles reduce the 13 sums over the warp (instead of 13 x 5); after the step with
-                        // lane-xor 16/8/4/2 each lane keeps half of its slots, so slot index = lane bits 4..1 and lanes 2i, 2i+1 both end
-                        // with the total of slot i
                         float v[16];
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) v[i] = i < 13 ? o[i] : 0.f;
-#pragma unroll
-                        for (int half = 8, bit = 16; half >= 1; half >>= 1, bit >>= 1) {
-                            const bool up = lane & bit;
-#pragma unroll
-                            for (int i = 0; i < half; ++i) {
-                                const float send = up ? v[i] : v[i + half], keep = up ? v[i + half] : v[i];
-                                v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
-                            }
-                        }
-                        float val = v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
-                        const int slot = lane >> 1;
+                        v[0] = fmaf(-gax, cx, g00); v[1] = fmaf(-gax, cy, g01); v[2] = fmaf(-gax, cz, g02);
+                        v[3] = fmaf(-gay, cx, g10); v[4] = fmaf(-gay, cy, g11); v[5] = fmaf(-gay, cz, g12);
+                        v[6] = fmaf(-gaz, cx, g20); v[7] = fmaf(-gaz, cy, g21); v[8] = fmaf(-gaz, cz, g22);
+                        v[9] = -(M00 * gax + M10 * gay + M20 * gaz);
+                        v[10] = -(M01 * gax + M11 * gay + M21 * gaz);
+                        v[11] = -(M02 * gax + M12 * gay + M22 * gaz);
+                        v[12] = gwa * alb;                                       // dL/dop      (gwa = dL/d(op * albedo) of this pair)
+                        v[13] = gwa * v0.w;                                      // dL/dalbedo  (degree 0: one albedo per Gaussian)
+                        v[14] = 0.f; v[15] = 0.f;
                         const int g = (int)(ent & ((1u << NLOS_ENTRY_SHIFT) - 1u));
-                        // slots: 0..8 dM, 9..11 dmu, 12 dop = alb * d(op*alb), 13 dalb = op * d(op*alb) (the two lanes of slot 12 write these)
-                        int dst = slot;
-                        bool wr = !(lane & 1) && slot < 12;
-                        if (slot == 12) { val *= (lane & 1) ? v0.w : v4.w; dst = 12 + (lane & 1); wr = true; }
-                        if (wr && val != 0.f) atomicAdd(P.dacc + (size_t)g * NLOS_GRAD_FLOATS + dst, val);
+                        const int slot = lane >> 1;
+                        if (P.sh_degree > 0) {
+                            // view-dependent albedo: dL/d(SH coefficients) = sum over the scan points of dpre Y_k(dir), and the direction's own
+                            // dependence on the mean goes into dL/dmu (slots 9..11)
+                            float dshv[16];
+                            const float dpre = alb > 0.f ? v[13] : 0.f;
+                            v[13] = 0.f;
+                            sh_pair_backward(P.sh + (size_t)g * P.sh_dim, P.sh_degree, cx, cy, cz, D, dpre, dshv, v[9], v[10], v[11]);
+                            const float sval = warp_reduce16(dshv, lane);
+                            if (!(lane & 1) && sval != 0.f) atomicAdd(P.dsh + (size_t)g * 16 + slot, sval);
+                        }
+                        // slots: 0..8 dM, 9..11 dmu, 12 dop, 13 dalb (degree 0)
+                        const float val = warp_reduce16(v, lane);
+                        if (!(lane & 1) && slot < 14 && val != 0.f) atomicAdd(P.dacc + (size_t)g * NLOS_GRAD_FLOATS + slot, val);
                     }
                 }
                 __syncwarp();

@@ -45,6 +45,9 @@ struct TransientParams {
     float* H;            // forward out   [n_tiles*32, T]  (accumulated with REDs; caller zeroes)
     const float* gH;     // backward in   [n_tiles*32, T]
     float* dacc;         // backward out  [N, 16]          (accumulated with REDs; caller zeroes)
+    const float* sh;     // raw SH coefficients [N, sh_dim] (used when sh_degree > 0: per (Gaussian, scan point) albedo, volume_renderer.cu:107-111)
+    int sh_dim, sh_degree;
+    float* dsh;          // backward out [N, 16]: dL/d(SH coefficients) when sh_degree > 0 (REDs; caller zeroes)
     unsigned char* hit_dump;        // tests only (nlosb200_debug_hit_dump): dense slab-test membership [n_tiles*32][A*A][N], or null
     unsigned long long* counters;   // MODE_COUNT: [0] hit (g,ray) pairs, [1] W_s, [2] evaluated sample-evals, [3] W_b
 };
@@ -94,6 +97,22 @@ __device__ __forceinline__ void stream_moments(f32x2 A, f32x2 B, f32x2 C, float 
     S0 += a0 + a1;
     S1 += b0 + b1;
     S2 += c0 + c1;
+}
+
+// transposing butterfly: 16 + 1 shuffles reduce 16 per-lane values over the warp (instead of 16 x 5); after the step with lane-xor 16/8/4/2
+// each lane keeps half of its slots, so slot index = lane bits 4..1 and lanes 2i, 2i+1 both return the total of slot i
+__device__ __forceinline__ float warp_reduce16(float (&v)[16], int lane)
+{
+#pragma unroll
+    for (int half = 8, bit = 16; half >= 1; half >>= 1, bit >>= 1) {
+        const bool up = lane & bit;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            const float send = up ? v[i] : v[i + half], keep = up ? v[i + half] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+        }
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
 // ---- host side, shared by the two kernels

@@ -45,9 +45,6 @@ class CUDARenderFunction(torch.autograd.Function):
         out = [None] * 15
         if not any(needs):
             return tuple(out)
-        if deg > 0 and (needs[0] or needs[4]):
-            raise RuntimeError("CUDARenderFunction.backward: view-dependent SH (active_sh_degree > 0) has no gradient kernel yet; "
-                               "the reference passes only the dc coefficient (cuda_autograd.py:280)")
         g = _C.render_rays_backward(ctx.prepared, ro, rd, ts, scales, rots, opac, feats, c, deltaT, mod, occ, rho, tr,
                                     grad_rho_density, grad_density, grad_transmittance)
         for i, (need, gi) in enumerate(zip(needs, g)):
@@ -71,9 +68,17 @@ class CUDARenderModule(nn.Module):
                 r_range: Tuple[float, float], num_theta: int, num_phi: int, num_r: int, c: float, deltaT: float,
                 scaling_modifier: float = 1.0, use_occlusion: bool = True, rendering_type: str = "netf"):
         origins, dirs, t_samples, theta_grid = ray_lattice(camera_pos, theta_range, phi_range, r_range, num_theta, num_phi, num_r)
+        # cuda_autograd.py:280 passes the dc coefficient only; with active_sh_degree > 0 the kernel needs (deg+1)^2 coefficients per
+        # Gaussian: take them from get_features ([N, K, 1] dc + rest) when the model has them, else _C evaluates degree 0 (documented)
+        feats = gaussian_model.get_features_dc.squeeze(1)
+        deg = int(gaussian_model.active_sh_degree)
+        if deg > 0 and hasattr(gaussian_model, "get_features"):
+            full = gaussian_model.get_features
+            full = full.reshape(full.shape[0], -1)
+            if full.shape[1] >= (deg + 1) ** 2:
+                feats = full[:, :(deg + 1) ** 2].contiguous()
         rho, _, _ = CUDARenderFunction.apply(origins, dirs, t_samples, gaussian_model.get_mu, gaussian_model._scaling,
-                                             gaussian_model._rotation, gaussian_model._opacity,
-                                             gaussian_model.get_features_dc.squeeze(1), camera_pos,
+                                             gaussian_model._rotation, gaussian_model._opacity, feats, camera_pos,
                                              gaussian_model.active_sh_degree, c, deltaT, scaling_modifier, use_occlusion, rendering_type)
         return attenuate_and_integrate(rho, t_samples, theta_grid, theta_range, phi_range)
 

@@ -68,7 +68,11 @@ class ShardedFitter:
 
     def step(self, means, log_scales, rotations, opacities, features):
         """-> (local loss contribution [tensor], grads tuple summed over all ranks)."""
-        reduce_fn = lambda d: all_reduce_packed(d, self.group)
+        def reduce_fn(d):
+            all_reduce_packed(d, self.group)
+            if getattr(self.r, "_deg", 0) > 0:                       # view-dependent albedo: the SH-coefficient gradients live in a second buffer
+                all_reduce_packed(self.r.dsh, self.group)
+            return d
         if self.fused:
             self.r.prepare(means, log_scales, rotations, opacities, features)
             Ht = self.r.forward_tiled()

@@ -33,7 +33,7 @@ class TransientRenderer:
     """Stateful renderer for one ScanGeometry: owns the preprocess / binning workspaces."""
 
     def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
-                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=1.6):
+                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=1.6, active_sh_degree=0):
         """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
         (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries a warp pulls at a time from its
         tile's counter (default: 16..256, sized so that every warp of the persistent grid gets >= 32 slices).
@@ -56,6 +56,9 @@ class TransientRenderer:
         self.n_buckets = -(-self.T // self.bucket)
         self.slice_len = slice_len
         self.mcut, self.mod, self.sigma = float(mcut), float(scaling_modifier), float(sigma_bbox)
+        # view-dependent albedo max(SH(dir(mu - o_p)) + 0.5, 0) per (Gaussian, scan point) (volume_renderer.cu:107-111); settable between steps
+        # like GaussianModel.active_sh_degree (main.py:240-241).  Needs features [N, >= (deg+1)^2]; a dc-only row falls back to degree 0 (_C.effective_sh_degree)
+        self.active_sh_degree = int(active_sh_degree)
         self.wpb = _lib.lib().nlosb200_transient_warps_per_block()
         self.n_classes = 2 if self.variant == 2 else 1
         self._N = None
@@ -105,12 +108,12 @@ class TransientRenderer:
         """Lazy overflow check of the PREVIOUS prepare(): its header copy finished long ago, so this does not stall the stream."""
         if self._pending is None:
             return
-        ev, gen = self._pending
+        ev, gen, capacity = self._pending
         self._pending = None
         ev.synchronize()
         total, overflow = int(self.header_host[0]), int(self.header_host[2])
         self.last_total = total
-        if overflow or total > self._list.numel():
+        if overflow or total > capacity:
             self._grow(total)
             raise ListOverflow(f"the entry lists of step {gen} ({total} entries) did not fit the list buffer: that step rendered nothing; "
                                "the buffer has been regrown, repeat the step")
@@ -131,6 +134,10 @@ class TransientRenderer:
         self._alloc(N, means.device)
         self._check_pending()
         self._params = (means, log_scales, rotations, opacities, features)
+        from ._C import effective_sh_degree
+        self._deg = effective_sh_degree(self.active_sh_degree, features.shape[1])
+        if self._deg > 0 and (getattr(self, "dsh", None) is None or self.dsh.shape[0] != N):
+            self.dsh = torch.empty(N, 16, dtype=torch.float32, device=means.device)
         self.generation += 1
         st = _lib.stream()
         _lib.call("nlosb200_preprocess", means.data_ptr(), log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(),
@@ -149,7 +156,7 @@ class TransientRenderer:
         self.header_host.copy_(self.header, non_blocking=True)
         ev = torch.cuda.Event()
         ev.record()
-        self._pending = (ev, self.generation)
+        self._pending = (ev, self.generation, self._list.numel())
 
     def check_lists(self):
         """Block until the last prepare() is known to have fitted its lists (raises ListOverflow otherwise) -> total entries."""
@@ -168,12 +175,16 @@ class TransientRenderer:
                 self._list_bins.data_ptr(), self._list.numel(), self.cell_offsets.data_ptr(), self.n_classes, cls, self.work.data_ptr(),
                 self.t0, self.dt, self.T, self.window, self.bucket, self._slice)
 
+    def _sh_args(self):
+        f = self._params[4]
+        return (f.data_ptr() if self._deg > 0 else None, f.shape[1], self._deg)
+
     def forward_tiled(self):
         """-> H [n_tiles*32, T] in tile-major scan order (after prepare())."""
         H = torch.empty(self.geom.n_tiles * TILE, self.T, dtype=torch.float32, device=self.records.device)
         for n, (cls, var) in enumerate(self._launches()):
-            _lib.call("nlosb200_transient_forward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, int(n > 0), H.data_ptr(),
-                      _lib.stream())
+            _lib.call("nlosb200_transient_forward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, int(n > 0),
+                      *self._sh_args(), H.data_ptr(), _lib.stream())
         return H
 
     def forward(self, means, log_scales, rotations, opacities, features):
@@ -185,7 +196,7 @@ class TransientRenderer:
         gH_tiled = _f32c(gH_tiled)
         for n, (cls, var) in enumerate(self._launches()):
             _lib.call("nlosb200_transient_backward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, int(n > 0),
-                      gH_tiled.data_ptr(), self.dacc.data_ptr(), _lib.stream())
+                      *self._sh_args(), gH_tiled.data_ptr(), self.dacc.data_ptr(), self.dsh.data_ptr() if self._deg > 0 else None, _lib.stream())
         return self.dacc
 
     def chain(self, params=None):
@@ -193,8 +204,13 @@ class TransientRenderer:
         means, log_scales, rotations, opacities, features = params if params is not None else self._params
         outs = [torch.empty_like(means), torch.empty_like(log_scales), torch.empty_like(rotations), torch.empty_like(opacities),
                 torch.empty_like(features)]
-        _lib.call("nlosb200_preprocess_backward", log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(), features.data_ptr(),
-                  self._N, features.shape[1], self.mod, self.dacc.data_ptr(), *[o.data_ptr() for o in outs], 0, _lib.stream())
+        if self._deg > 0:
+            _lib.call("nlosb200_preprocess_backward_sh", log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(), features.data_ptr(),
+                      self._N, features.shape[1], self._deg, self.mod, self.dacc.data_ptr(), self.dsh.data_ptr(), *[o.data_ptr() for o in outs], 0,
+                      _lib.stream())
+        else:
+            _lib.call("nlosb200_preprocess_backward", log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(), features.data_ptr(),
+                      self._N, features.shape[1], self.mod, self.dacc.data_ptr(), *[o.data_ptr() for o in outs], 0, _lib.stream())
         return tuple(outs)
 
     def backward_tiled(self, gH_tiled, reduce_fn=None):

@@ -61,12 +61,22 @@ def filter_gaussians(ray_o, ray_d, bbox):
 
 def render_rays(ray_o, ray_d, t_samples, means, log_scales, rots, opac, feats, cam,
                 sh_degree=0, c=1.0, deltaT=0.01, scaling_modifier=1.0, use_occlusion=True,
-                rendering_type="netf", return_filter=False):
+                rendering_type="netf", return_filter=False, filter_lists=None):
+    """filter_lists int32 [n_rays, 257]: render with these per-ray lists instead of filtering (frozen membership)."""
     ray_o, ray_d, t_samples = _f(ray_o), _f(ray_d), _f(t_samples)
     means, log_scales, rots, opac, feats, cam = _f(means), _f(log_scales), _f(rots), _f(opac).reshape(-1), _f(feats), _f(cam)
     n_rays, T, N = ray_o.shape[0], t_samples.shape[0], means.shape[0]
     feats = feats.reshape(N, -1)
     outs = [np.empty((n_rays, T), np.float32) for _ in range(3)]
+    if filter_lists is not None:
+        fl = np.ascontiguousarray(filter_lists, np.int32)
+        assert fl.shape == (n_rays, cap() + 1)
+        lib().ref_render_rays_with_filter(_p(ray_o), _p(ray_d), _p(t_samples), _p(means), _p(log_scales), _p(rots), _p(opac),
+                                          _p(feats), _p(cam), C.c_int(n_rays), C.c_int(T), C.c_int(N), C.c_int(sh_degree),
+                                          C.c_int(feats.shape[1]), C.c_float(c), C.c_float(deltaT), C.c_float(scaling_modifier),
+                                          C.c_int(int(use_occlusion)), C.c_int(0 if rendering_type == "netf" else 1), _p(fl),
+                                          _p(outs[0]), _p(outs[1]), _p(outs[2]))
+        return tuple(outs)
     filt = np.empty((n_rays, cap() + 1), np.int32) if return_filter else None
     lib().ref_render_rays(_p(ray_o), _p(ray_d), _p(t_samples), _p(means), _p(log_scales), _p(rots), _p(opac),
                           _p(feats), _p(cam), C.c_int(n_rays), C.c_int(T), C.c_int(N), C.c_int(sh_degree),

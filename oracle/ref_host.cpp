@@ -86,6 +86,23 @@ void ref_render_rays(const float *ro, const float *rd, const float *t_samples,
     });
 }
 
+/* the same kernel with the per-ray lists GIVEN (frozen ray membership: finite differences of the reference forward must not move rays in
+ * or out of a 3-sigma AABB -- the hard cull is a discontinuity of the reference) */
+void ref_render_rays_with_filter(const float *ro, const float *rd, const float *t_samples,
+                                 const float *means, const float *scales, const float *rots, const float *opac,
+                                 const float *feats, const float *cam, int n_rays, int T, int N, int sh_degree, int sh_dim,
+                                 float c, float deltaT, float mod, int use_occlusion, int rendering_type, const int *filter /*[n_rays,257]*/,
+                                 float *rho, float *density, float *trans)
+{
+    std::memset(rho, 0, sizeof(float) * (size_t)n_rays * T);
+    std::memset(density, 0, sizeof(float) * (size_t)n_rays * T);
+    std::memset(trans, 0, sizeof(float) * (size_t)n_rays * T);
+    launch_1d(n_rays, [&] {
+        volume_render_kernel(ro, rd, t_samples, filter, means, scales, rots, opac, feats, cam, n_rays, T, N,
+                             sh_degree, sh_dim, c, deltaT, mod, use_occlusion != 0, rendering_type, rho, density, trans);
+    });
+}
+
 /* volume_renderer_analytic.cu:178-241 */
 void ref_render_rays_analytic(const float *ro, const float *rd, float t_min, float t_max, const int *filter,
                               const float *means, const float *scales, const float *rots, const float *opac,

@@ -24,6 +24,30 @@ def quat_to_rotmat(q):
     return R.reshape(-1, 3, 3)
 
 
+def sh_basis(deg, v):
+    """[...,3] unit vectors -> [..., (deg+1)^2]: real SH polynomials, the all-positive sign convention of spherical_harmonics.cuh:20-53."""
+    x, y, z = v.unbind(-1)
+    Y = [torch.full_like(x, C0)]
+    if deg >= 1:
+        Y += [0.4886025119029199 * y, 0.4886025119029199 * z, 0.4886025119029199 * x]
+    if deg >= 2:
+        Y += [1.0925484305920792 * x * y, 1.0925484305920792 * y * z, 0.31539156525252005 * (3 * z * z - 1), 1.0925484305920792 * x * z,
+              0.5462742152960396 * (x * x - y * y)]
+    if deg >= 3:
+        Y += [0.5900435899266435 * y * (3 * x * x - y * y), 2.890611442640554 * x * y * z, 0.4570457994644658 * y * (5 * z * z - 1),
+              0.3731763325901154 * z * (5 * z * z - 3), 0.4570457994644658 * x * (5 * z * z - 1), 1.445305721320277 * z * (x * x - y * y),
+              0.5900435899266435 * x * (x * x - 3 * y * y)]
+    return torch.stack(Y, -1)
+
+
+def view_albedo(means, feats, cam, deg):
+    """max(SH(dir(mu - cam)) + 0.5, 0), dir = c / (|c| + 1e-8)   (volume_renderer.cu:107-111, cuda_utils.cuh:48-51)."""
+    c = means - cam[None, :]
+    v = c / (c.norm(dim=1, keepdim=True) + 1e-8)
+    K = (deg + 1) ** 2
+    return torch.clamp_min((sh_basis(deg, v) * feats.reshape(feats.shape[0], -1)[:, :K]).sum(-1) + 0.5, 0.0)
+
+
 def activate(means, log_scales, rots, opac, feats, mod=1.0):
     R = quat_to_rotmat(rots)
     s = torch.exp(log_scales) * mod
@@ -58,7 +82,7 @@ def ray_values(o, d, t, mask, means, M, op, mode, dt_lat):
 
 
 def transient_batch(scan_o, sin_th, cos_th, sin_ph, cos_ph, t, hscale, masks, means, log_scales, rots, opac, feats,
-                    c, deltaT, mod=1.0, mode=0):
+                    c, deltaT, mod=1.0, mode=0, sh_degree=0):
     """H [S,T]; masks [S, A*A, N] bool (ray r = i*A + j)."""
     M, op, alb = activate(means, log_scales, rots, opac, feats, mod)
     S, A = sin_th.shape
@@ -70,7 +94,8 @@ def transient_batch(scan_o, sin_th, cos_th, sin_ph, cos_ph, t, hscale, masks, me
                          (sin_th[p][:, None] * sin_ph[p][None, :]).reshape(-1),
                          cos_th[p][:, None].expand(A, A).reshape(-1)], 1)
         v = ray_values(scan_o[p], d, t, masks[p], means, M, op, mode, dt_lat)       # [R,N,T]
-        rho = (v * alb[None, :, None]).sum(1)                                        # [R,T]
+        a_p = alb if sh_degree == 0 else view_albedo(means, feats, scan_o[p], sh_degree)     # per (Gaussian, scan point)
+        rho = (v * a_p[None, :, None]).sum(1)                                         # [R,T]
         if mode == 0:
             rho = rho * c * deltaT
         w = sin_th[p][:, None].expand(A, A).reshape(-1)
@@ -78,9 +103,11 @@ def transient_batch(scan_o, sin_th, cos_th, sin_ph, cos_ph, t, hscale, masks, me
     return torch.stack(out)
 
 
-def render_rays(ray_o, ray_d, t, mask, means, log_scales, rots, opac, feats, c, deltaT, mod=1.0, use_occlusion=False):
-    """(rho, density, transmittance) [R,T] of volume_renderer.cu for rays sharing one origin (degree-0 SH)."""
+def render_rays(ray_o, ray_d, t, mask, means, log_scales, rots, opac, feats, c, deltaT, mod=1.0, use_occlusion=False, sh_degree=0, cam=None):
+    """(rho, density, transmittance) [R,T] of volume_renderer.cu for rays sharing one origin; sh_degree > 0: albedo of camera `cam`."""
     M, op, alb = activate(means, log_scales, rots, opac, feats, mod)
+    if sh_degree > 0:
+        alb = view_albedo(means, feats, cam, sh_degree)
     v = ray_values(ray_o[0], ray_d, t, mask, means, M, op, 0, None)               # pdf*op  [R,N,T]
     density = v.sum(1)
     if not use_occlusion:

@@ -18,10 +18,10 @@ def np32(t):
     return t.detach().cpu().numpy().astype(np.float32)
 
 
-def oracle_H(geom, ta, params, mode=0, precision="f64", use_occlusion=False, cap=0, count=False):
+def oracle_H(geom, ta, params, mode=0, precision="f64", use_occlusion=False, cap=0, count=False, sh_degree=0):
     means, ls, rots, opac, feats = [np32(p) for p in params]
     return oracle.transient_batch(np32(geom.scan_o), np32(geom.sin_th), np32(geom.cos_th), np32(geom.sin_ph), np32(geom.cos_ph),
-                                  np32(ta["t_samples"]), np32(geom.hscale), means, ls, rots, opac, feats, sh_degree=0,
+                                  np32(ta["t_samples"]), np32(geom.hscale), means, ls, rots, opac, feats, sh_degree=sh_degree,
                                   c=ta["c"], deltaT=ta["deltaT"], scaling_modifier=1.0, use_occlusion=use_occlusion, mode=mode,
                                   cap=cap, exp_mode=1, precision=precision, count=count)
 
