@@ -146,6 +146,24 @@ int nlosb200_render_rays_analytic(const float* ray_origins, const float* ray_dir
                                   int n_rays, int N, int sh_dim, int sh_degree, float scaling_modifier, float sigma_threshold,
                                   int max_sections, float* out, void* stream);
 
+/* ==== batched transient WITH occlusion (per-ray semantics of the reference: the first `cap` = 256 Gaussians in index order per ray,
+ * src/ray_aabb.cu:10-61; shared transmittance with the early stop at 1e-4, src/volume_renderer.cu:80-137; attenuation + angular sum,
+ * gaussian_model/cuda_autograd.py:302-314; x vp_y^2, nlos_helpers.py:275-276) for the scan points [sp0, sp0 + n_sp) of the tile-major grid
+ * (row P of H = tile P/32, lane P%32).  Nothing of size [rays, T] is materialised.
+ *   lists int32 [n_sp][A*A][cap+1] (nlosb200_occluded_list_ints): column 0 = count, then ASCENDING Gaussian ids = the reference's per-ray lists;
+ *   t_samples [T] = the radii (uniform: t0 + k dt); c_deltaT = c * deltaT; mcut: samples with Mahalanobis distance > mcut are skipped;
+ *   use_occlusion 0 renders the no-occlusion branch (:139-182) on the same capped lists; sh / sh_dim / sh_degree as nlosb200_transient_forward.
+ * forward ADDS to H [n_tiles*32, T]; backward ADDS to dacc [N,16] (and dsh [N,16] when sh_degree > 0): the caller zeroes them.  A <= 64, T <= 2048. */
+long long nlosb200_occluded_list_ints(int n_scan_points, int A, int cap);
+int nlosb200_occluded_lists(const float* tiles, int n_tiles, int A, const float* records, int N, int cap, int sp0, int n_sp, int* lists,
+                            void* stream);
+int nlosb200_occluded_forward(const float* tiles, int n_tiles, int A, const float* records, int N, int cap, const int* lists, int sp0,
+                              int n_sp, const float* t_samples, int T, float t0, float dt, float c_deltaT, float mcut, int use_occlusion,
+                              const float* sh, int sh_dim, int sh_degree, float* H, void* stream);
+int nlosb200_occluded_backward(const float* tiles, int n_tiles, int A, const float* records, int N, int cap, const int* lists, int sp0,
+                               int n_sp, const float* t_samples, int T, float t0, float dt, float c_deltaT, float mcut, int use_occlusion,
+                               const float* sh, int sh_dim, int sh_degree, const float* grad_H, float* dacc, float* dsh, void* stream);
+
 /* ==== fused squared-error loss of the batched fitting step (nlos_helpers.py:280-346 compute_loss, per scan point in the reference; its
  * batched variant nlos_helpers.py:348-351 is an empty stub): loss += inv_numel * sum (H - target)^2 ; grad_H = 2 inv_numel (H - target)
  * on the tile-major layout of nlosb200_transient_forward.  n % 4 == 0, 16-byte aligned; loss is ONE double, accumulated (caller zeroes);
@@ -165,6 +183,11 @@ int nlosb200_adam_step(int n_tensors, float* const* params, const float* const* 
  * nlosb200_preprocess (+ nlosb200_compat_albedo for a camera-dependent albedo).  Outputs [n_points], overwritten. */
 int nlosb200_evaluate_points(const float* points, long long n_points, const float* records, int N, float* density, float* rho_density,
                              void* stream);
+/* records for nlosb200_evaluate_points in the DENSE PyTorch semantics gaussian2volume actually runs: scale = exp(exp(_scaling) *
+ * scaling_modifier) (gaussian_model.py:265), R (x - mu) instead of R^T (x - mu) (:281-282), no epsilon, degree-0 albedo.  Only mean,
+ * sigmoid(opacity), M and albedo are filled. */
+int nlosb200_preprocess_dense(const float* means, const float* log_scales, const float* rotations, const float* opacities,
+                              const float* features, int N, int sh_dim, float scaling_modifier, float* records, void* stream);
 
 /* ==== scale-initialisation helper: simple-knn's distCUDA2 (gaussian_model/gaussian_model.py:7-11,202-203; the submodule is pinned at
  * 60f461f in .SUBMODULES.json but absent from the tree).  out[i] = mean of the squared distances from point i to its 3 nearest OTHER

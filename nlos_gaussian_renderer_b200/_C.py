@@ -189,11 +189,17 @@ def render_rays_analytic(ray_origins, ray_directions, t_min, t_max, gaussian_fil
 
 
 def evaluate_points(points, gaussian_means, gaussian_scales, gaussian_rotations, gaussian_opacities, gaussian_features, camera_pos=None,
-                    active_sh_degree=0, scaling_modifier=1.0):
+                    active_sh_degree=0, scaling_modifier=1.0, semantics="cuda"):
     """Dense evaluation at `points` [Na,3] -> (rho_density [Na], density [Na]): sums over ALL Gaussians, the quantities
     GaussianModel.estimate_rho_w_no_occlusion(..., out_separately=True) returns (gaussian_model/gaussian_model.py:346-364) and
     gaussian2volume samples (nlos_helpers.py:40-69), with the CUDA renderer's pdf arithmetic (include/cuda_utils.cuh:124-151).
-    camera_pos None -> degree-0 albedo; else the view-dependent albedo of that position (volume_renderer.cu:107-111)."""
+    camera_pos None -> degree-0 albedo; else the view-dependent albedo of that position (volume_renderer.cu:107-111).
+    semantics="dense": the arithmetic gaussian2volume really evaluates in the reference -- GaussianModel.estimate_gaussian_pdf
+    (gaussian_model.py:253-294): scale = exp(exp(_scaling) * mod), R (x - mu), no epsilon (SURVEY App. A.1 column a), degree-0 albedo --
+    so that a model fitted with the reference's dense path is sampled with ITS pdf; "cuda" (default) = the CUDA renderer's pdf, i.e.
+    what this library's renderers fit."""
+    if semantics not in ("cuda", "dense"):
+        raise ValueError("semantics must be 'cuda' or 'dense'")
     for t, n in ((points, "points"), (gaussian_means, "gaussian_means"), (gaussian_scales, "gaussian_scales"),
                  (gaussian_rotations, "gaussian_rotations"), (gaussian_opacities, "gaussian_opacities"), (gaussian_features, "gaussian_features")):
         _check(t, n)
@@ -202,7 +208,12 @@ def evaluate_points(points, gaussian_means, gaussian_scales, gaussian_rotations,
     feats = gaussian_features.reshape(N, -1) if N else gaussian_features.reshape(0, 1)
     records = _aligned(max(N, 1) * L.nlosb200_record_floats(), torch.float32, dev, 128)
     st = _lib.stream()
-    if N:
+    if N and semantics == "dense":
+        if camera_pos is not None and int(active_sh_degree) > 0:
+            raise RuntimeError("evaluate_points(semantics='dense') implements the degree-0 albedo only")
+        _lib.call("nlosb200_preprocess_dense", gaussian_means.data_ptr(), gaussian_scales.data_ptr(), gaussian_rotations.data_ptr(),
+                  gaussian_opacities.data_ptr(), feats.data_ptr(), N, feats.shape[1], float(scaling_modifier), records.data_ptr(), st)
+    elif N:
         _lib.call("nlosb200_preprocess", gaussian_means.data_ptr(), gaussian_scales.data_ptr(), gaussian_rotations.data_ptr(),
                   gaussian_opacities.data_ptr(), feats.data_ptr(), N, feats.shape[1], float(scaling_modifier), 3.0, 0.0, records.data_ptr(),
                   None, None, st)

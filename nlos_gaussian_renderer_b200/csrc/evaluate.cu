@@ -75,6 +75,48 @@ __global__ void __launch_bounds__(EV_THREADS) evaluate_points_kernel(const float
         }
 }
 
+// ---- records in the DENSE PyTorch semantics (SURVEY.md App. A.1 column a), which is what gaussian2volume actually evaluates in the reference:
+//      gaussian_model.py:265      scales = exp(get_scaling * scaling_modifier) = exp(exp(_scaling) * mod)   (double activation)
+//      gaussian_model.py:281-282  T = R (x - mu)  (R, not R^T), no epsilon on the scales; build_rotation has no zero-norm guard (gaussian_utils.py:189-210)
+//      gaussian_model.py:310,359  albedo = clamp_min(C0 * f_dc + 0.5, 0) at degree 0
+// Only the fields nlosb200_evaluate_points reads are meaningful (mean, sigmoid(opacity), M = diag(1/s) R, albedo).
+__global__ void __launch_bounds__(256) preprocess_dense_kernel(const float* __restrict__ means, const float* __restrict__ log_scales,
+                                                               const float* __restrict__ rots, const float* __restrict__ opac,
+                                                               const float* __restrict__ feats, int N, int sh_dim, float mod, float* __restrict__ records)
+{
+    int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= N) return;
+    float w = rots[4 * g], x = rots[4 * g + 1], y = rots[4 * g + 2], z = rots[4 * g + 3];
+    const float inv = 1.0f / sqrtf(w * w + x * x + y * y + z * z);
+    w *= inv; x *= inv; y *= inv; z *= inv;
+    const float R[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y),
+                        2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x),
+                        2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)};
+    float is[3];
+    for (int j = 0; j < 3; ++j) is[j] = 1.0f / expf(expf(log_scales[3 * g + j]) * mod);
+    const float op = 1.0f / (1.0f + expf(-opac[g]));
+    const float alb = fmaxf(fmaf(NLOS_SH_C0, feats[(size_t)g * sh_dim], 0.5f), 0.0f);
+    float4* rec = reinterpret_cast<float4*>(records + (size_t)g * NLOS_REC_FLOATS);
+    rec[0] = make_float4(means[3 * g], means[3 * g + 1], means[3 * g + 2], op);
+    rec[1] = make_float4(R[0] * is[0], R[1] * is[0], R[2] * is[0], R[3] * is[1]);       // row j of M = row j of R / s_j
+    rec[2] = make_float4(R[4] * is[1], R[5] * is[1], R[6] * is[2], R[7] * is[2]);
+    rec[3] = make_float4(R[8] * is[2], 0.f, 0.f, 0.f);
+    rec[4] = make_float4(0.f, 0.f, 0.f, alb);
+    rec[5] = make_float4(0.f, 0.f, 0.f, 0.f); rec[6] = rec[5]; rec[7] = rec[5];
+}
+
+extern "C" int nlosb200_preprocess_dense(const float* means, const float* log_scales, const float* rotations, const float* opacities,
+                                         const float* features, int N, int sh_dim, float scaling_modifier, float* records, void* stream)
+{
+    if (N <= 0) return 0;
+    NLOS_REQUIRE(means && log_scales && rotations && opacities && features && records && sh_dim >= 1, "preprocess_dense: null pointer");
+    NLOS_REQUIRE(((uintptr_t)records % 16) == 0, "preprocess_dense: records must be 16-byte aligned");
+    preprocess_dense_kernel<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(means, log_scales, rotations, opacities, features, N, sh_dim,
+                                                                               scaling_modifier, records);
+    NLOS_CHECK_LAUNCH("preprocess_dense_kernel");
+    return 0;
+}
+
 // points [n_points,3]; records [N,32] from nlosb200_preprocess (degree-0 albedo) optionally followed by nlosb200_compat_albedo (view-dependent
 // albedo of one camera position); density, rho_density [n_points] (overwritten).
 extern "C" int nlosb200_evaluate_points(const float* points, long long n_points, const float* records, int N,

@@ -89,7 +89,7 @@ def test_batched_slice_equals_per_scan_point_operator(mode_occl):
 
 @pytest.mark.parametrize("occl", [True, False])
 def test_occluded_batch_equals_per_scan_point_loop(occl):
-    """render_transient_batch_occluded (one operator call per chunk of scan points) == the reference's loop of CUDARenderModule.forward over
+    """render_transient_batch_occluded (native batched kernels, csrc/occluded.cu) == the reference's loop of CUDARenderModule.forward over
     the scan points (main.py:198-203) times vp_y^2 (nlos_helpers.py:275-276), values and parameter gradients."""
     from nlos_gaussian_renderer_b200.dropin.cuda_autograd import CUDARenderModule
     from nlos_gaussian_renderer_b200.occluded import render_transient_batch_occluded
@@ -100,7 +100,7 @@ def test_occluded_batch_equals_per_scan_point_loop(occl):
     r0, r1 = ta["start"] * ta["c"] * ta["deltaT"], ta["end"] * ta["c"] * ta["deltaT"]
     t_samples = torch.linspace(r0, r1, T, device="cuda")
     pa = [p.clone().requires_grad_() for p in params]
-    H = render_transient_batch_occluded(geom, t_samples, *pa, ta["c"], ta["deltaT"], use_occlusion=occl, chunk_scan_points=4)
+    H = render_transient_batch_occluded(geom, t_samples, *pa, ta["c"], ta["deltaT"], use_occlusion=occl, chunk_scan_points=32)
     assert tuple(H.shape) == (Sy, Sx, T)
     wgt = torch.linspace(0.5, 1.5, Sy * Sx * T, device="cuda").reshape(Sy, Sx, T)
     (H * wgt).sum().backward()

@@ -41,3 +41,33 @@ def test_evaluate_points_equals_one_sample_of_render_rays():
     assert float(rho_e[0]) > 0.1
     assert abs(float(rho_r[0, 0]) / 0.01 - float(rho_e[0])) <= 1e-4 * float(rho_e[0])
     assert abs(float(dens_r[0, 0]) - float(dens_e[0])) <= 1e-4 * float(dens_e[0])
+
+
+def test_evaluate_points_dense_semantics_matches_the_reference_dense_port():
+    """semantics="dense" == the reference's dense PyTorch arithmetic (estimate_gaussian_pdf / estimate_rho_w_no_occlusion,
+    gaussian_model.py:253-294,346-364: scale = exp(exp(s) mod), R not R^T) -- checked against oracle/dense_torch.py, which
+    tests/test_ref_python.py pins to the reference's own output."""
+    from oracle import dense_torch
+    N, Na = 300, 2000
+    g = torch.Generator().manual_seed(4)
+    means = torch.tensor([0.0, 0.75, 0.0]) + (torch.rand(N, 3, generator=g) - 0.5) * 0.4
+    ls = torch.log(torch.log(1.0 + 0.02 + 0.06 * torch.rand(N, 3, generator=g)))       # exp(exp(ls)) - 1 ~ 2-8 cm ... in the dense semantics s ~ 1.02-1.08
+    rots = torch.randn(N, 4, generator=g)
+    opac = torch.randn(N, 1, generator=g)
+    fdc = (0.2 * torch.rand(N, 1, generator=g) - 0.5) / 0.28209479177387814
+    x = torch.tensor([0.0, 0.75, 0.0]) + (torch.rand(Na, 3, generator=g) - 0.5) * 3.0
+    rho, dens = _C.evaluate_points(x.cuda(), means.cuda(), ls.cuda(), rots.cuda(), opac.cuda(), fdc.cuda(), semantics="dense", scaling_modifier=0.9)
+    # the port evaluates sum_g pdf op alb on a lattice: feed the points as a [Na,1,1] lattice with unit attenuation
+    s = torch.exp(torch.exp(ls.double()) * 0.9)
+    R = dense_torch.build_rotation(rots.double())
+    loc = torch.einsum("gij,gnj->gni", R, x.double()[None] - means.double()[:, None]) / s[:, None, :]
+    pdf = torch.exp(-0.5 * (loc * loc).sum(-1))
+    op = torch.sigmoid(opac.double().reshape(-1))
+    alb = torch.clamp_min(0.28209479177387814 * fdc.double().reshape(-1) + 0.5, 0.0)
+    want_d, want_r = (pdf * op[:, None]).sum(0), (pdf * (op * alb)[:, None]).sum(0)
+    assert float(want_d.max()) > 1.0
+    assert float((dens.cpu().double() - want_d).abs().max()) <= 2e-5 * float(want_d.max())
+    assert float((rho.cpu().double() - want_r).abs().max()) <= 2e-5 * float(want_r.max())
+    # and the two semantics differ (SURVEY App. A.1): same inputs, CUDA pdf
+    rho_c, _ = _C.evaluate_points(x.cuda(), means.cuda(), ls.cuda(), rots.cuda(), opac.cuda(), fdc.cuda(), scaling_modifier=0.9)
+    assert float((rho_c - rho).abs().max()) > 0.1 * float(rho.max())
