@@ -94,7 +94,12 @@ int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const fl
                                 const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                 int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
                                 int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree,
-                                const float* grad_H, float* dacc, float* dsh, void* stream);
+                                const float* grad_H, float* dacc, float* dsh, int per_tile_partials, void* stream);
+/* Deterministic mode (bit-identical results run to run): the float REDs of the render kernels are the only order-dependent operations.
+ * Forward: launch with slice_len >= the longest tile list, so that ONE warp walks a tile's list in order and is the only writer of the tile's
+ * rows of H.  Backward: additionally per_tile_partials = 1 with dacc (and dsh) = [n_tiles][N][16] partial buffers -- every tile accumulates into
+ * its own copy -- followed by nlosb200_reduce_tile_partials, which sums them in tile order into [N][16]. */
+int nlosb200_reduce_tile_partials(const float* partial, int n_tiles, long long n, float* out, void* stream);
 /* counters uint64 [4]: hit (g,ray) pairs, W_s, sample-evals evaluated, W_b */
 int nlosb200_transient_count(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                              const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,

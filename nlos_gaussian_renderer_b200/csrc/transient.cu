@@ -809,11 +809,11 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                             v[13] = 0.f;
                             sh_pair_backward(P.sh + (size_t)g * P.sh_dim, P.sh_degree, cx, cy, cz, D, dpre, dshv, v[9], v[10], v[11]);
                             const float sval = warp_reduce16(dshv, lane);
-                            if (!(lane & 1) && sval != 0.f) atomicAdd(P.dsh + (size_t)g * 16 + slot, sval);
+                            if (!(lane & 1) && sval != 0.f) atomicAdd(P.dsh + (size_t)tile * P.part_stride + (size_t)g * 16 + slot, sval);
                         }
                         // slots: 0..8 dM, 9..11 dmu, 12 dop, 13 dalb (degree 0)
                         const float val = warp_reduce16(v, lane);
-                        if (!(lane & 1) && slot < 14 && val != 0.f) atomicAdd(P.dacc + (size_t)g * NLOS_GRAD_FLOATS + slot, val);
+                        if (!(lane & 1) && slot < 14 && val != 0.f) atomicAdd(P.dacc + (size_t)tile * P.part_stride + (size_t)g * NLOS_GRAD_FLOATS + slot, val);
                     }
                 }
                 __syncwarp();
@@ -889,7 +889,7 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
     P.cpt = n_classes * P.n_buckets; P.cell0 = cls * P.n_buckets;
     P.slice_len = slice_len; P.flush_scale = mode == MODE_NUM ? c_deltaT : 1.0f; P.mcut2 = mcut * mcut;
     P.H = nullptr; P.gH = nullptr; P.dacc = nullptr; P.counters = nullptr; P.hit_dump = g_hit_dump;
-    P.sh = sh; P.sh_dim = sh_dim; P.sh_degree = sh_degree; P.dsh = nullptr;
+    P.sh = sh; P.sh_dim = sh_dim; P.sh_degree = sh_degree; P.dsh = nullptr; P.part_stride = 0;
     return 0;
 }
 
@@ -920,7 +920,7 @@ extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int 
                                            const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                            int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
                                            int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree,
-                                           const float* grad_H, float* dacc, float* dsh, void* stream)
+                                           const float* grad_H, float* dacc, float* dsh, int per_tile_partials, void* stream)
 {
     TransientParams P;
     int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
@@ -928,17 +928,19 @@ extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int 
     if (rc) return rc;
     NLOS_REQUIRE(grad_H && dacc && (sh_degree == 0 || dsh), "transient_backward: null pointer");
     cudaStream_t s = (cudaStream_t)stream;
+    const size_t n_part = per_tile_partials ? (size_t)n_tiles : 1;
     if (!accumulate) {
-        cudaError_t e = cudaMemsetAsync(dacc, 0, (size_t)N * NLOS_GRAD_FLOATS * sizeof(float), s);
+        cudaError_t e = cudaMemsetAsync(dacc, 0, n_part * N * NLOS_GRAD_FLOATS * sizeof(float), s);
         NLOS_REQUIRE(e == cudaSuccess, "transient_backward: memset: %s", cudaGetErrorString(e));
         if (sh_degree > 0) {
-            e = cudaMemsetAsync(dsh, 0, (size_t)N * 16 * sizeof(float), s);
+            e = cudaMemsetAsync(dsh, 0, n_part * N * 16 * sizeof(float), s);
             NLOS_REQUIRE(e == cudaSuccess, "transient_backward: memset: %s", cudaGetErrorString(e));
         }
     }
     P.gH = grad_H;
     P.dacc = dacc;
     P.dsh = dsh;
+    P.part_stride = per_tile_partials ? (size_t)N * NLOS_GRAD_FLOATS : 0;
     if (variant == 1) return launch_transient_narrow(P, mode, true, s);
     return mode == MODE_NUM ? launch_transient<MODE_NUM, true>(P, s, "transient_kernel<num,bwd>")
                             : launch_transient<MODE_ANA, true>(P, s, "transient_kernel<ana,bwd>");
@@ -962,4 +964,22 @@ extern "C" int nlosb200_transient_count(const float* tiles, int n_tiles, int A, 
     }
     P.counters = counters;
     return launch_transient<MODE_COUNT, false>(P, s, "transient_kernel<count>");
+}
+
+// deterministic mode: out[i] = sum over the tiles, IN TILE ORDER, of partial[tile][i]   (n = N * 16 floats per tile)
+__global__ void __launch_bounds__(256) reduce_tile_partials_kernel(const float* __restrict__ partial, int n_tiles, long long n, float* __restrict__ out)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float a = 0.f;
+    for (int t = 0; t < n_tiles; ++t) a += partial[(size_t)t * n + i];
+    out[i] = a;
+}
+
+extern "C" int nlosb200_reduce_tile_partials(const float* partial, int n_tiles, long long n, float* out, void* stream)
+{
+    NLOS_REQUIRE(partial && out && n_tiles > 0 && n > 0, "reduce_tile_partials: bad arguments");
+    reduce_tile_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(partial, n_tiles, n, out);
+    NLOS_CHECK_LAUNCH("reduce_tile_partials_kernel");
+    return 0;
 }

@@ -794,11 +794,11 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                             v[13] = 0.f;
                             sh_pair_backward(P.sh + (size_t)g * P.sh_dim, P.sh_degree, cx, cy, cz, D, dpre, dshv, v[9], v[10], v[11]);
                             const float sval = warp_reduce16(dshv, lane);
-                            if (!(lane & 1) && sval != 0.f) atomicAdd(P.dsh + (size_t)g * 16 + slot, sval);
+                            if (!(lane & 1) && sval != 0.f) atomicAdd(P.dsh + (size_t)tile * P.part_stride + (size_t)g * 16 + slot, sval);
                         }
                         // slots: 0..8 dM, 9..11 dmu, 12 dop, 13 dalb (degree 0)
                         const float val = warp_reduce16(v, lane);
-                        if (!(lane & 1) && slot < 14 && val != 0.f) atomicAdd(P.dacc + (size_t)g * NLOS_GRAD_FLOATS + slot, val);
+                        if (!(lane & 1) && slot < 14 && val != 0.f) atomicAdd(P.dacc + (size_t)tile * P.part_stride + (size_t)g * NLOS_GRAD_FLOATS + slot, val);
                     }
                 }
                 __syncwarp();

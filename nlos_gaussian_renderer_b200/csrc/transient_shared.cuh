@@ -47,6 +47,7 @@ struct TransientParams {
     float* dacc;         // backward out  [N, 16]          (accumulated with REDs; caller zeroes)
     const float* sh;     // raw SH coefficients [N, sh_dim] (used when sh_degree > 0: per (Gaussian, scan point) albedo, volume_renderer.cu:107-111)
     int sh_dim, sh_degree;
+    size_t part_stride;  // 0, or N*16: deterministic mode -- dacc / dsh are per-TILE partial buffers [n_tiles][N][16], summed in tile order afterwards
     float* dsh;          // backward out [N, 16]: dL/d(SH coefficients) when sh_degree > 0 (REDs; caller zeroes)
     unsigned char* hit_dump;        // tests only (nlosb200_debug_hit_dump): dense slab-test membership [n_tiles*32][A*A][N], or null
     unsigned long long* counters;   // MODE_COUNT: [0] hit (g,ray) pairs, [1] W_s, [2] evaluated sample-evals, [3] W_b

@@ -33,7 +33,8 @@ class TransientRenderer:
     """Stateful renderer for one ScanGeometry: owns the preprocess / binning workspaces."""
 
     def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
-                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=1.6, active_sh_degree=0):
+                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=1.6, active_sh_degree=0,
+                 deterministic=False):
         """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
         (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries a warp pulls at a time from its
         tile's counter (default: 16..256, sized so that every warp of the persistent grid gets >= 32 slices).
@@ -59,6 +60,10 @@ class TransientRenderer:
         # view-dependent albedo max(SH(dir(mu - o_p)) + 0.5, 0) per (Gaussian, scan point) (volume_renderer.cu:107-111); settable between steps
         # like GaussianModel.active_sh_degree (main.py:240-241).  Needs features [N, >= (deg+1)^2]; a dc-only row falls back to degree 0 (_C.effective_sh_degree)
         self.active_sh_degree = int(active_sh_degree)
+        # deterministic=True: bit-identical H and gradients run to run ("deterministic mode, no float atomics, so that races show up
+        # as non-reproducibility").  One warp walks a whole tile list in order (no work stealing inside a tile) and the backward accumulates
+        # into per-tile partial buffers [n_tiles, N, 16] that are summed in tile order.  Slower and memory-hungry: a debugging mode.
+        self.deterministic = bool(deterministic)
         self.wpb = _lib.lib().nlosb200_transient_warps_per_block()
         self.n_classes = 2 if self.variant == 2 else 1
         self._N = None
@@ -98,6 +103,9 @@ class TransientRenderer:
                 self._slice = self._slice // 4 * 4
         else:
             self._slice = int(self.slice_len)
+        if self.deterministic:
+            self._slice = 1 << 30
+            self.dacc_part = torch.empty(self.geom.n_tiles, N, L.nlosb200_grad_floats(), dtype=torch.float32, device=dev)
 
     def _bin_args(self):
         g = self.geom
@@ -138,6 +146,8 @@ class TransientRenderer:
         self._deg = effective_sh_degree(self.active_sh_degree, features.shape[1])
         if self._deg > 0 and (getattr(self, "dsh", None) is None or self.dsh.shape[0] != N):
             self.dsh = torch.empty(N, 16, dtype=torch.float32, device=means.device)
+            if self.deterministic:
+                self.dsh_part = torch.empty(self.geom.n_tiles, N, 16, dtype=torch.float32, device=means.device)
         self.generation += 1
         st = _lib.stream()
         _lib.call("nlosb200_preprocess", means.data_ptr(), log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(),
@@ -194,9 +204,16 @@ class TransientRenderer:
     def render_backward(self, gH_tiled):
         """transient backward kernels only: dL/dH (tile-major) -> the packed [N,16] gradient buffer self.dacc."""
         gH_tiled = _f32c(gH_tiled)
+        det = self.deterministic
+        dacc = self.dacc_part if det else self.dacc
+        dsh = (self.dsh_part if det else self.dsh) if self._deg > 0 else None
         for n, (cls, var) in enumerate(self._launches()):
             _lib.call("nlosb200_transient_backward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, int(n > 0),
-                      *self._sh_args(), gH_tiled.data_ptr(), self.dacc.data_ptr(), self.dsh.data_ptr() if self._deg > 0 else None, _lib.stream())
+                      *self._sh_args(), gH_tiled.data_ptr(), dacc.data_ptr(), dsh.data_ptr() if dsh is not None else None, int(det), _lib.stream())
+        if det:
+            _lib.call("nlosb200_reduce_tile_partials", dacc.data_ptr(), self.geom.n_tiles, self.dacc.numel(), self.dacc.data_ptr(), _lib.stream())
+            if dsh is not None:
+                _lib.call("nlosb200_reduce_tile_partials", dsh.data_ptr(), self.geom.n_tiles, self.dsh.numel(), self.dsh.data_ptr(), _lib.stream())
         return self.dacc
 
     def chain(self, params=None):

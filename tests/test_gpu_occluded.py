@@ -110,7 +110,7 @@ def test_early_stop_and_cap_in_a_dense_opaque_scene():
     H64 = util.oracle_H(scenes_cpu(geom), tb, [p.cpu() for p in params], mode=0, precision="f64", use_occlusion=True, cap=256)
     Hu = util.oracle_H(scenes_cpu(geom), tb, [p.cpu() for p in params], mode=0, precision="f64", use_occlusion=True, cap=0)
     assert util.rel_to_max(Hu, H64) > 1e-3                                        # the cap changes the result here
-    assert (H64[:, -8:] == 0).all() and H64.max() > 0                             # fully occluded tail
+    assert H64[:, -8:].max() < 1e-9 * H64.max() and H64.max() > 0                 # occluded tail
     assert util.rel_to_max(H.cpu().numpy().reshape(-1, T), H64) < 2e-4
 
 

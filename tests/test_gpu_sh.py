@@ -62,7 +62,7 @@ def test_batched_backward_matches_autograd(deg, mode, variant):
         ga, gb = a.grad.cpu().numpy(), b.grad.numpy()
         assert util.rel_to_max(ga, gb) < TOL, name
         if name == "features":
-            assert np.abs(gb[:, 1:K]).max() > 0 and np.abs(ga[:, K:]).max() == 0
+            assert np.abs(gb[:, 1:K]).max() > 0 and (K == 16 or np.abs(ga[:, K:]).max() == 0)
 
 
 @pytest.mark.parametrize("deg", [1, 2, 3])

@@ -97,3 +97,27 @@ def test_list_overflow_is_detected_one_step_later():
         r.check_lists()                                              # ... and says so
     H3 = r.forward(*params)                                          # the buffer has been regrown
     assert torch.equal(H3, H1) or util.rel_to_max(H3.cpu().numpy(), H1.cpu().numpy()) < 1e-6
+
+
+@pytest.mark.parametrize("mode", ["numerical", "analytic"])
+def test_deterministic_mode_is_bit_reproducible(mode):
+    """deterministic=True: H and every gradient are bit-identical run to run (the default mode accumulates with float REDs in scheduling order and
+    is only reproducible to rounding); and it agrees with the default mode to rounding."""
+    N, Sy, Sx, T, A = 500, 8, 16, 128, 8
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=1.5, device="cuda")
+    feats = (torch.randn(N, 16, generator=torch.Generator().manual_seed(3)) * 0.3).cuda()
+    params = list(params[:4]) + [feats]
+    gH = torch.rand(Sy, Sx, T, generator=torch.Generator().manual_seed(2)).cuda()
+    runs = []
+    for rep in range(3):
+        r = _r(geom, ta, mode, deterministic=rep < 2, active_sh_degree=2, window=64, bucket=8)
+        ps = [p.clone().requires_grad_() for p in params]
+        H = render_transient_batch(r, *ps)
+        (H * gH).sum().backward()
+        runs.append((H.detach().clone(), [p.grad.clone() for p in ps]))
+    assert torch.equal(runs[0][0], runs[1][0])
+    for a, b in zip(runs[0][1], runs[1][1]):
+        assert torch.equal(a, b)
+    assert util.rel_to_max(runs[2][0].cpu().numpy(), runs[0][0].cpu().numpy()) < 1e-5
+    for a, b in zip(runs[2][1], runs[0][1]):
+        assert util.rel_to_max(a.cpu().numpy(), b.cpu().numpy()) < 2e-5
