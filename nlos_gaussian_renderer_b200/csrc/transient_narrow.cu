@@ -12,7 +12,7 @@
 //   * backward: as transient.cu (prefix-sum moments against the window's weights, one butterfly reduction per entry).
 #include "transient_shared.cuh"
 
-template <int MODE, bool BWD>
+template <int MODE, bool BWD, bool SH>
 __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(const TransientParams P)
 {
     constexpr bool FWD = !BWD;
@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     // ---- the pair (this lane's scan point): radial reject against the entry's bins, AABB relative to the scan point, a = M (o - mu)
                     const float D = sqrtf(d2);
                     float alb = v4.w;                                                                       // degree-0 albedo of the record
-                    if (P.sh_degree > 0)                                                                    // view-dependent: one albedo per (Gaussian, scan point)
+                    if (SH)                                                                                 // view-dependent: one albedo per (Gaussian, scan point)
                         alb = sh_pair_albedo(P.sh + (size_t)(ent & ((1u << NLOS_ENTRY_SHIFT) - 1u)) * P.sh_dim, P.sh_degree, cx, cy, cz, D);
                     const float opalb = v0.w * alb;
                     const bool act = valid && opalb > 0.f && (D + v5.x >= r_in) && (D - v5.x <= r_out);
@@ -786,13 +786,15 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                         v[14] = 0.f; v[15] = 0.f;
                         const int g = (int)(ent & ((1u << NLOS_ENTRY_SHIFT) - 1u));
                         const int slot = lane >> 1;
-                        if (P.sh_degree > 0) {
+                        if (SH) {
                             // view-dependent albedo: dL/d(SH coefficients) = sum over the scan points of dpre Y_k(dir), and the direction's own
                             // dependence on the mean goes into dL/dmu (slots 9..11)
                             float dshv[16];
                             const float dpre = alb > 0.f ? v[13] : 0.f;
                             v[13] = 0.f;
-                            sh_pair_backward(P.sh + (size_t)g * P.sh_dim, P.sh_degree, cx, cy, cz, D, dpre, dshv, v[9], v[10], v[11]);
+                            float gmx = 0.f, gmy = 0.f, gmz = 0.f;          // (scalars: v[] must not have its address taken, it lives in registers)
+                            sh_pair_backward(P.sh + (size_t)g * P.sh_dim, P.sh_degree, cx, cy, cz, D, dpre, dshv, gmx, gmy, gmz);
+                            v[9] += gmx; v[10] += gmy; v[11] += gmz;
                             const float sval = warp_reduce16(dshv, lane);
                             if (!(lane & 1) && sval != 0.f) atomicAdd(P.dsh + (size_t)tile * P.part_stride + (size_t)g * 16 + slot, sval);
                         }
@@ -815,17 +817,18 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
 }
 
 // ---- launch (called by the C-ABI entry points in transient.cu)
-template <int MODE, bool BWD>
+template <int MODE, bool BWD, bool SH = false>
 static int launch_narrow(const TransientParams& P, cudaStream_t s, const char* name)
 {
+    if (!SH && P.sh_degree > 0) return launch_narrow<MODE, BWD, true>(P, s, name);     // view-dependent albedo: its own instantiation
     int n_sm = transient_num_sms();
     cudaError_t em = cudaMemsetAsync(P.work, 0, (size_t)P.n_tiles * sizeof(int), s);
     NLOS_REQUIRE(em == cudaSuccess, "%s: memset: %s", name, cudaGetErrorString(em));
     size_t smem = transient_smem_bytes(P.A, P.window);
     NLOS_REQUIRE(smem <= 227 * 1024, "%s: %zu B of shared memory needed (A=%d, window=%d) > 227 KB", name, smem, P.A, P.window);
-    cudaError_t e = cudaFuncSetAttribute(transient_narrow_kernel<MODE, BWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(transient_narrow_kernel<MODE, BWD, SH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     NLOS_REQUIRE(e == cudaSuccess, "%s: cudaFuncSetAttribute: %s", name, cudaGetErrorString(e));
-    transient_narrow_kernel<MODE, BWD><<<n_sm, TR_WPB * 32, smem, s>>>(P);
+    transient_narrow_kernel<MODE, BWD, SH><<<n_sm, TR_WPB * 32, smem, s>>>(P);
     NLOS_CHECK_LAUNCH(name);
     return 0;
 }
