@@ -197,12 +197,16 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __
                                                                  unsigned* __restrict__ list, unsigned* __restrict__ list_bins, long long capacity,
                                                                  long long* __restrict__ header)
 {
+    // ordered fill without a loop over the cells: every entry sets the bit of its Gaussian's index inside the chunk in the bitmap of its cell
+    // (shared memory), a prefix over the bitmap words gives each entry its rank among the chunk's entries of the same cell in ascending
+    // Gaussian index -- the order oracle.window_lists defines
     __shared__ TilePoints tp;
-    __shared__ int wc[BIN_GPT][BIN_THREADS / 32][2 * BIN_MAX_RANGES];
+    __shared__ unsigned bm[2 * BIN_MAX_RANGES][BIN_CHUNK / 32];
+    __shared__ unsigned short pre[2 * BIN_MAX_RANGES][BIN_CHUNK / 32];
     int tile = blockIdx.y, chunk = blockIdx.x;
     const int cpt = n_classes * n_buckets;
-    int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     load_tile_points(tp, tiles, tile, A);
+    for (int i = threadIdx.x; i < 2 * BIN_MAX_RANGES * (BIN_CHUNK / 32); i += BIN_THREADS) (&bm[0][0])[i] = 0u;
     __syncthreads();
     int lo[BIN_GPT], hi[BIN_GPT], cl[BIN_GPT];
 #pragma unroll
@@ -212,38 +216,29 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __
         hi[j] = 0;
         cl[j] = 0;
         if (g < N) shell_bins(tp, shell[g], t0, inv_dt, T, L, narrow_k, rad_k, lo[j], hi[j], cl[j]);
+        const int li = j * BIN_THREADS + threadIdx.x;                     // index inside the chunk, ascending with g
+        for (int s = lo[j]; s <= hi[j]; s += L) atomicOr(&bm[cl[j] * n_buckets + s / bucket][li >> 5], 1u << (li & 31));
     }
-#pragma unroll
-    for (int j = 0; j < BIN_GPT; ++j)
-        for (int c = 0; c < cpt; ++c) {
-            const int r = c < n_buckets ? c : c - n_buckets, k = c < n_buckets ? 0 : 1;
-            unsigned b = __ballot_sync(0xffffffffu, cl[j] == k && entry_in_bucket(lo[j], hi[j], r, L, bucket) >= 0);
-            if (lane == 0) wc[j][warp][c] = __popc(b);
-        }
     __syncthreads();
     if (threadIdx.x < cpt) {
-        int r = threadIdx.x, run = 0;
-        for (int j = 0; j < BIN_GPT; ++j)
-            for (int w = 0; w < BIN_THREADS / 32; ++w) { int v = wc[j][w][r]; wc[j][w][r] = run; run += v; }
+        unsigned run = 0;
+        for (int w = 0; w < BIN_CHUNK / 32; ++w) { pre[threadIdx.x][w] = (unsigned short)run; run += __popc(bm[threadIdx.x][w]); }
     }
     __syncthreads();
-    unsigned lt = (1u << lane) - 1u;
 #pragma unroll
     for (int j = 0; j < BIN_GPT; ++j) {
         int g = chunk * BIN_CHUNK + j * BIN_THREADS + threadIdx.x;
-        for (int c = 0; c < cpt; ++c) {
-            const int r = c < n_buckets ? c : c - n_buckets, k = c < n_buckets ? 0 : 1;
-            int e = cl[j] == k ? entry_in_bucket(lo[j], hi[j], r, L, bucket) : -1;
-            unsigned b = __ballot_sync(0xffffffffu, e >= 0);
-            if (e >= 0) {
-                size_t cell = (size_t)tile * cpt + c;
-                long long pos = cell_offsets[cell] + chunk_off[cell * n_chunks + chunk] + wc[j][warp][c] + __popc(b & lt);
-                if (pos < capacity) {
-                    list[pos] = (unsigned)g | ((unsigned)e << NLOS_ENTRY_SHIFT);
-                    if (list_bins) list_bins[pos] = (unsigned)lo[j] | ((unsigned)hi[j] << 16);      // the Gaussian's tile-level shell [klo, khi]
-                }
-                else header[2] = 1;
-            }
+        const int li = j * BIN_THREADS + threadIdx.x;
+        int e = 0;
+        for (int s = lo[j]; s <= hi[j]; s += L, ++e) {
+            const int c = cl[j] * n_buckets + s / bucket;
+            const size_t cell = (size_t)tile * cpt + c;
+            const long long pos = cell_offsets[cell] + chunk_off[cell * n_chunks + chunk] + pre[c][li >> 5] +
+                                  __popc(bm[c][li >> 5] & ((1u << (li & 31)) - 1u));
+            if (pos < capacity) {
+                list[pos] = (unsigned)g | ((unsigned)e << NLOS_ENTRY_SHIFT);
+                if (list_bins) list_bins[pos] = (unsigned)lo[j] | ((unsigned)hi[j] << 16);      // the Gaussian's tile-level shell [klo, khi]
+            } else header[2] = 1;
         }
     }
 }
