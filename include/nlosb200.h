@@ -26,10 +26,11 @@ int nlosb200_bin_num_chunks(int N);
 /* ---- per-Gaussian activation / packing -------------------------------------------------------
  * Replaces compute_gaussian_bboxes_kernel (include/bbox_compute.cuh:76-120) and the per-sample
  * re-activation inside volume_render_kernel (src/volume_renderer.cu:86-111).
- * records [N,32] (128-B aligned), shell [N,4] = (mean, mcut*max scale), bboxes [N,6]; each nullable. */
+ * records [N,32] (128-B aligned), shell [N,4] = (mean, mcut*max scale; negated when the smallest scale is >= time_wide_min > 0: the
+ * "time-wide" flag of the window binning), bboxes [N,6]; each nullable. */
 int nlosb200_preprocess(const float* means, const float* log_scales, const float* rotations, const float* opacities,
                         const float* features, int N, int sh_dim, float scaling_modifier, float sigma_bbox, float mcut,
-                        float* records, float* shell, float* bboxes, void* stream);
+                        float time_wide_min, float* records, float* shell, float* bboxes, void* stream);
 /* dacc [N,16] = {dL/dM(9), dL/dmu(3), dL/dop, dL/dalb0, 0, 0} -> raw parameter gradients
  * (the backward the reference leaves as zeros, gaussian_model/cuda_autograd.py:139-172). */
 int nlosb200_preprocess_backward(const float* log_scales, const float* rotations, const float* opacities, const float* features,
@@ -62,14 +63,16 @@ int nlosb200_build_scan_tiles(const float* scan_o, const float* sin_th, const fl
  * n_buckets = ceil(T/bucket) <= 64.  Entry classes: with n_classes = 2 the cells of a tile are class-major (n_cells = n_tiles * n_classes *
  * n_buckets, cell = tile * 2 n_buckets + cls * n_buckets + bucket); an entry is class 0 ("narrow") when its Gaussian is listed once in the tile
  * and (6 / mcut) rad <= narrow_rays * pitch * min-distance, pitch = the smallest lattice step of the tile's scan points -- i.e. its 3-sigma AABB
- * spans at most narrow_rays lattice pitches -- else class 1.  n_classes = 1 (narrow_rays = 0): a single class.
+ * spans at most narrow_rays lattice pitches -- else class 1 (narrow_rays = 0: no footprint classes).  time_wide = 1 adds an independent class
+ * bit: the shell carries the time-wide flag (nlosb200_preprocess) and the interval keeps 3 bins from both ends of the time axis.  Class index =
+ * footprint bit + n_fp * time bit; n_classes = n_fp * n_tw must be passed consistently (1, 2 or 4).
  * chunk_counts int32 [n_cells * nlosb200_bin_num_chunks(N)], cell_counts int32 [n_cells], cell_offsets int64 [n_cells+1],
  * tile_items int32 [n_tiles+1], header int64 [4] = {total list entries, CTA work items, overflow flag, -}. */
 int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                             int window, int bucket, int n_classes, float narrow_rays, float mcut, int slice_len, int warps_per_block,
+                             int window, int bucket, int n_classes, float narrow_rays, float mcut, int time_wide, int slice_len, int warps_per_block,
                              int* chunk_counts, int* cell_counts, long long* cell_offsets, int* tile_items, long long* header, void* stream);
 int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                             int window, int bucket, int n_classes, float narrow_rays, float mcut, const int* chunk_counts_scanned,
+                             int window, int bucket, int n_classes, float narrow_rays, float mcut, int time_wide, const int* chunk_counts_scanned,
                              const long long* cell_offsets, int* list, int* list_bins, long long list_capacity, long long* header,
                              void* stream);
 
@@ -89,12 +92,18 @@ int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float
 int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                               int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H, void* stream);
+                               int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H, void* stream);
 int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                 const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                 int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                                int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree,
+                                int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree,
                                 const float* grad_H, float* dacc, float* dsh, int per_tile_partials, void* stream);
+/* One-pass analytic plan (mode 1, launches over the TIME-WIDE entry classes of the binning: smallest scale >= 1.3 bins): one_pass = 1 renders
+ * every ray with the 1-node mixture and leaves the 1/(r^2+1e-8) weight out -- H is then a buffer Ha of unweighted rows, and
+ *   forward : nlosb200_analytic_filter(Ha, H, rows, T, t0, dt, 0)   adds  w F(Ha)  to H   (F = the fixed 7-tap filter that turns 1-node rows into
+ *             bin integrals to <= 1.6e-5 of a ray's peak; w = 1/(r^2+1e-8));
+ *   backward: nlosb200_analytic_filter(gH, gHa, rows, T, t0, dt, 1) gives  gHa = F(w gH), the grad_H of the one_pass = 1 backward launches. */
+int nlosb200_analytic_filter(const float* in, float* out, long long rows, int T, float t0, float dt, int backward, void* stream);
 /* Deterministic mode (bit-identical results run to run): the float REDs of the render kernels are the only order-dependent operations.
  * Forward: launch with slice_len >= the longest tile list, so that ONE warp walks a tile's list in order and is the only writer of the tile's
  * rows of H.  Backward: additionally per_tile_partials = 1 with dacc (and dsh) = [n_tiles][N][16] partial buffers -- every tile accumulates into

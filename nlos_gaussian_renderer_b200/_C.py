@@ -98,7 +98,7 @@ def _prepare(ray_origins, ray_directions, means, scales, rotations, opacities, f
     if N:
         # sigma is hard-coded 3.0 inside render_rays (volume_renderer.cu:232,244); mcut unused here
         _lib.call("nlosb200_preprocess", means.data_ptr(), scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(), feats.data_ptr(),
-                  N, P.sh_dim, float(scaling_modifier), 3.0, 0.0, P.records.data_ptr(), None, P.bboxes.data_ptr(), st)
+                  N, P.sh_dim, float(scaling_modifier), 3.0, 0.0, 0.0, P.records.data_ptr(), None, P.bboxes.data_ptr(), st)
         _lib.call("nlosb200_compat_albedo", means.data_ptr(), feats.data_ptr(), camera_pos.data_ptr(), N, P.sh_dim, int(sh_degree),
                   P.records.data_ptr(), st)
     P.camera_pos, P.means = camera_pos, means
@@ -215,7 +215,7 @@ def evaluate_points(points, gaussian_means, gaussian_scales, gaussian_rotations,
                   gaussian_opacities.data_ptr(), feats.data_ptr(), N, feats.shape[1], float(scaling_modifier), records.data_ptr(), st)
     elif N:
         _lib.call("nlosb200_preprocess", gaussian_means.data_ptr(), gaussian_scales.data_ptr(), gaussian_rotations.data_ptr(),
-                  gaussian_opacities.data_ptr(), feats.data_ptr(), N, feats.shape[1], float(scaling_modifier), 3.0, 0.0, records.data_ptr(),
+                  gaussian_opacities.data_ptr(), feats.data_ptr(), N, feats.shape[1], float(scaling_modifier), 3.0, 0.0, 0.0, records.data_ptr(),
                   None, None, st)
         if camera_pos is not None:
             _check(camera_pos, "camera_pos")

@@ -16,7 +16,10 @@
 // class 0 ("narrow": rendered by transient_narrow.cu) when the Gaussian is listed once in the tile (interval <= L) and its 3-sigma AABB
 // spans at most `narrow_rays` lattice pitches of the tile:  (6 / mcut) rad <= narrow_rays * pitch * sqrt(min_p |mu - o_p|^2) , with
 // rad = mcut max(scale) from the shell and pitch = the smallest angular step (dtheta, dphi) of the tile's scan points; otherwise class 1.
-// Same single-rounding operation order in oracle/__init__.py:entry_classes.
+// Same single-rounding operation order in oracle/__init__.py:entry_classes.  A second, independent class bit (time_wide = 1): the Gaussian's
+// smallest scale is at least 1.3 bins (flag = sign bit of the shell radius, set by nlosb200_preprocess), it is listed once in the tile and
+// its interval keeps 3 bins from both ends of the time axis -- every ray of such an entry is a ONE-node ray of the analytic-exact mode (transient.cu, one-pass plan).
+// Class index = footprint bit + n_fp * time bit, n_classes = n_fp * n_tw in {1, 2, 4}.
 //
 // Passes (all stream ordered, no host sync inside):
 //   count : per (tile, chunk of 1024 Gaussians) histogram of cell membership
@@ -32,6 +35,7 @@ using namespace nlos;
 #define BIN_THREADS 256
 #define BIN_GPT (BIN_CHUNK / BIN_THREADS)
 #define BIN_MAX_RANGES 64
+#define BIN_MAX_CLASSES 4
 
 struct TilePoints {
     float ox[NLOS_TILE], oy[NLOS_TILE], oz[NLOS_TILE];
@@ -58,6 +62,8 @@ __device__ __forceinline__ void load_tile_points(TilePoints& tp, const float* __
 __device__ __forceinline__ void shell_bins(const TilePoints& tp, float4 sh, float t0, float inv_dt, int T, int L, float narrow_k, float rad_k,
                                            int& klo, int& khi, int& cls)
 {
+    const bool tw_flag = sh.w < 0.f;           // time-wide Gaussian (preprocess); rad_k < 0 says the flag takes part in the class index
+    sh.w = fabsf(sh.w);
     float d2min = INFINITY, d2max = 0.0f, pitch = INFINITY;
 #pragma unroll 8
     for (int l = 0; l < NLOS_TILE; ++l) {
@@ -74,10 +80,13 @@ __device__ __forceinline__ void shell_bins(const TilePoints& tp, float4 sh, floa
     klo = klo_f < 0.0f ? 0 : (klo_f > (float)(T - 1) ? T : (int)klo_f);
     khi = khi_f < 0.0f ? -1 : (khi_f > (float)(T - 1) ? T - 1 : (int)khi_f);
     cls = 0;
+    int n_fp = 1;
     if (narrow_k > 0.f) {
-        bool narrow = khi - klo + 1 <= L && __fmul_rn(sh.w, rad_k) <= __fmul_rn(__fmul_rn(narrow_k, pitch), __fsqrt_rn(d2min));
+        bool narrow = khi - klo + 1 <= L && __fmul_rn(sh.w, fabsf(rad_k)) <= __fmul_rn(__fmul_rn(narrow_k, pitch), __fsqrt_rn(d2min));
         cls = narrow ? 0 : 1;
+        n_fp = 2;
     }
+    if (rad_k < 0.f && tw_flag && klo >= 3 && khi <= T - 4 && khi - klo + 1 <= L) cls += n_fp;
 }
 
 // sub-interval index e of the entry of [klo, khi] that lives in bucket r, or -1  (L > bucket => at most one)
@@ -96,10 +105,10 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_count_kernel(const float* _
                                                                   int n_classes, float narrow_k, float rad_k, int* __restrict__ chunk_counts)
 {
     __shared__ TilePoints tp;
-    __shared__ int cnt[2 * BIN_MAX_RANGES];
+    __shared__ int cnt[BIN_MAX_CLASSES * BIN_MAX_RANGES];
     int tile = blockIdx.y, chunk = blockIdx.x;
     load_tile_points(tp, tiles, tile, A);
-    if (threadIdx.x < 2 * BIN_MAX_RANGES) cnt[threadIdx.x] = 0;
+    if (threadIdx.x < BIN_MAX_CLASSES * BIN_MAX_RANGES) cnt[threadIdx.x] = 0;
     __syncthreads();
 #pragma unroll
     for (int j = 0; j < BIN_GPT; ++j) {
@@ -201,12 +210,13 @@ __global__ void __launch_bounds__(BIN_THREADS) shell_fill_kernel(const float* __
     // (shared memory), a prefix over the bitmap words gives each entry its rank among the chunk's entries of the same cell in ascending
     // Gaussian index -- the order oracle.window_lists defines
     __shared__ TilePoints tp;
-    __shared__ unsigned bm[2 * BIN_MAX_RANGES][BIN_CHUNK / 32];
-    __shared__ unsigned short pre[2 * BIN_MAX_RANGES][BIN_CHUNK / 32];
+    extern __shared__ __align__(16) unsigned char fill_smem[];        // bitmaps [cpt][32] words + word prefixes [cpt][32] shorts
     int tile = blockIdx.y, chunk = blockIdx.x;
     const int cpt = n_classes * n_buckets;
+    unsigned (*bm)[BIN_CHUNK / 32] = reinterpret_cast<unsigned (*)[BIN_CHUNK / 32]>(fill_smem);
+    unsigned short (*pre)[BIN_CHUNK / 32] = reinterpret_cast<unsigned short (*)[BIN_CHUNK / 32]>(fill_smem + (size_t)cpt * (BIN_CHUNK / 32) * 4);
     load_tile_points(tp, tiles, tile, A);
-    for (int i = threadIdx.x; i < 2 * BIN_MAX_RANGES * (BIN_CHUNK / 32); i += BIN_THREADS) (&bm[0][0])[i] = 0u;
+    for (int i = threadIdx.x; i < cpt * (BIN_CHUNK / 32); i += BIN_THREADS) (&bm[0][0])[i] = 0u;
     __syncthreads();
     int lo[BIN_GPT], hi[BIN_GPT], cl[BIN_GPT];
 #pragma unroll
@@ -256,25 +266,28 @@ static int check_window(const char* who, int T, int window, int bucket, int N)
     return 0;
 }
 
-static int check_classes(const char* who, int n_classes, float narrow_rays, float mcut)
+// rad_k: |rad_k| = 6 / mcut (footprint class), sign = the time-wide flag of the shell takes part in the class index
+static int check_classes(const char* who, int n_classes, float narrow_rays, float mcut, int time_wide, float& rad_k)
 {
-    NLOS_REQUIRE(n_classes == 1 || n_classes == 2, "%s: n_classes=%d must be 1 or 2", who, n_classes);
-    NLOS_REQUIRE(n_classes == 1 ? narrow_rays == 0.f : narrow_rays > 0.f, "%s: narrow_rays must be > 0 with two classes and 0 with one", who);
-    NLOS_REQUIRE(n_classes == 1 || mcut > 0.f, "%s: mcut must be > 0", who);
+    NLOS_REQUIRE(narrow_rays >= 0.f && (time_wide == 0 || time_wide == 1), "%s: bad class arguments", who);
+    const int want = (narrow_rays > 0.f ? 2 : 1) * (time_wide ? 2 : 1);
+    NLOS_REQUIRE(n_classes == want, "%s: n_classes=%d but narrow_rays=%g, time_wide=%d give %d", who, n_classes, narrow_rays, time_wide, want);
+    NLOS_REQUIRE(mcut > 0.f, "%s: mcut must be > 0", who);
+    rad_k = (time_wide ? -1.0f : 1.0f) * 6.0f / mcut;
     return 0;
 }
 
 extern "C" int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                                        int window, int bucket, int n_classes, float narrow_rays, float mcut, int slice_len, int warps_per_block,
+                                        int window, int bucket, int n_classes, float narrow_rays, float mcut, int time_wide, int slice_len, int warps_per_block,
                                         int* chunk_counts, int* cell_counts, long long* cell_offsets, int* tile_items, long long* header,
                                         void* stream)
 {
     NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0 && slice_len > 0 && warps_per_block > 0, "bin_window_plan: bad sizes");
     int rc = check_window("bin_window_plan", T, window, bucket, N);
     if (rc) return rc;
-    rc = check_classes("bin_window_plan", n_classes, narrow_rays, mcut);
+    float rad_k;
+    rc = check_classes("bin_window_plan", n_classes, narrow_rays, mcut, time_wide, rad_k);
     if (rc) return rc;
-    const float rad_k = n_classes == 2 ? 6.0f / mcut : 0.f;
     int n_buckets = (T + bucket - 1) / bucket;
     NLOS_REQUIRE(n_tiles <= 65535, "bin_window_plan: n_tiles=%d > 65535 (shard the scan grid)", n_tiles);
     NLOS_REQUIRE(tiles && shell && chunk_counts && cell_counts && cell_offsets && tile_items && header, "bin_window_plan: null pointer");
@@ -293,22 +306,25 @@ extern "C" int nlosb200_bin_window_plan(const float* tiles, int n_tiles, int A, 
 }
 
 extern "C" int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float* shell, int N, float t0, float dt, int T,
-                                        int window, int bucket, int n_classes, float narrow_rays, float mcut, const int* chunk_counts_scanned,
+                                        int window, int bucket, int n_classes, float narrow_rays, float mcut, int time_wide, const int* chunk_counts_scanned,
                                         const long long* cell_offsets, int* list, int* list_bins, long long list_capacity, long long* header,
                                         void* stream)
 {
     NLOS_REQUIRE(n_tiles > 0 && N > 0 && T > 0, "bin_window_fill: bad sizes");
     int rc = check_window("bin_window_fill", T, window, bucket, N);
     if (rc) return rc;
-    rc = check_classes("bin_window_fill", n_classes, narrow_rays, mcut);
+    float rad_k;
+    rc = check_classes("bin_window_fill", n_classes, narrow_rays, mcut, time_wide, rad_k);
     if (rc) return rc;
-    const float rad_k = n_classes == 2 ? 6.0f / mcut : 0.f;
     int n_buckets = (T + bucket - 1) / bucket;
     NLOS_REQUIRE(list || list_capacity == 0, "bin_window_fill: null list");
     NLOS_REQUIRE(!list_bins || T <= 65535, "bin_window_fill: list_bins packs two 16-bit bins (T=%d)", T);
     int n_chunks = (N + BIN_CHUNK - 1) / BIN_CHUNK;
     float inv_dt = 1.0f / dt;
-    shell_fill_kernel<<<dim3(n_chunks, n_tiles), BIN_THREADS, 0, (cudaStream_t)stream>>>(
+    const size_t fill_smem = (size_t)n_classes * n_buckets * (BIN_CHUNK / 32) * 6;
+    cudaError_t ea = cudaFuncSetAttribute(shell_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fill_smem);
+    NLOS_REQUIRE(ea == cudaSuccess, "bin_window_fill: cudaFuncSetAttribute: %s", cudaGetErrorString(ea));
+    shell_fill_kernel<<<dim3(n_chunks, n_tiles), BIN_THREADS, fill_smem, (cudaStream_t)stream>>>(
         tiles, A, reinterpret_cast<const float4*>(shell), N, t0, inv_dt, T, window - bucket, bucket, n_buckets, n_chunks, n_classes, narrow_rays,
         rad_k, chunk_counts_scanned, cell_offsets, reinterpret_cast<unsigned*>(list), reinterpret_cast<unsigned*>(list_bins), list_capacity, header);
     NLOS_CHECK_LAUNCH("shell_fill_kernel");

@@ -33,7 +33,7 @@ using namespace nlos;
 __global__ void __launch_bounds__(256) preprocess_kernel(const float* __restrict__ means, const float* __restrict__ log_scales,
                                                          const float* __restrict__ rots, const float* __restrict__ opac,
                                                          const float* __restrict__ feats, int N, int sh_dim, float mod,
-                                                         float sigma, float mcut, float* __restrict__ records,
+                                                         float sigma, float mcut, float tw_min, float* __restrict__ records,
                                                          float4* __restrict__ shell, float* __restrict__ bboxes)
 {
     int g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -56,7 +56,8 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const float* __restrict
         b[3] = bmax[0]; b[4] = bmax[1]; b[5] = bmax[2];
     }
     float rad = __fmul_rn(mcut, fmaxf(fmaxf(sx, sy), sz));
-    if (shell) shell[g] = make_float4(mx, my, mz, rad);
+    // the sign bit of the shell radius flags a time-wide Gaussian: smallest scale >= tw_min (= 1.3 bins; 0 switches the flag off)
+    if (shell) shell[g] = make_float4(mx, my, mz, (tw_min > 0.f && fminf(fminf(sx, sy), sz) >= tw_min) ? -rad : rad);
     if (!records) return;
     // cuda_utils.cuh:124-151 : t = R^T (x - mu), m2 = sum (t_j / (s_j + 1e-8))^2
     float is0 = 1.0f / (sx + 1e-8f), is1 = 1.0f / (sy + 1e-8f), is2 = 1.0f / (sz + 1e-8f);
@@ -78,14 +79,14 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const float* __restrict
 
 extern "C" int nlosb200_preprocess(const float* means, const float* log_scales, const float* rotations, const float* opacities,
                                    const float* features, int N, int sh_dim, float scaling_modifier, float sigma_bbox, float mcut,
-                                   float* records, float* shell, float* bboxes, void* stream)
+                                   float time_wide_min, float* records, float* shell, float* bboxes, void* stream)
 {
     if (N <= 0) return 0;
     NLOS_REQUIRE(means && log_scales && rotations, "preprocess: null parameter pointer");
     NLOS_REQUIRE(!records || (opacities && features && sh_dim >= 1), "preprocess: records need opacities and features");
     NLOS_REQUIRE(!records || ((uintptr_t)records % 128) == 0, "preprocess: records must be 128-byte aligned");
     preprocess_kernel<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(means, log_scales, rotations, opacities, features, N, sh_dim,
-                                                                         scaling_modifier, sigma_bbox, mcut, records,
+                                                                         scaling_modifier, sigma_bbox, mcut, time_wide_min, records,
                                                                          reinterpret_cast<float4*>(shell), bboxes);
     NLOS_CHECK_LAUNCH("preprocess_kernel");
     return 0;
@@ -214,7 +215,7 @@ extern "C" int nlosb200_compute_bboxes(const float* means, const float* log_scal
     if (N <= 0) return 0;
     NLOS_REQUIRE(means && log_scales && rotations && bboxes, "compute_bboxes: null pointer");
     preprocess_kernel<<<(N + 255) / 256, 256, 0, (cudaStream_t)stream>>>(means, log_scales, rotations, nullptr, nullptr, N, 1, scaling_modifier,
-                                                                         sigma, 0.f, nullptr, nullptr, bboxes);
+                                                                         sigma, 0.f, 0.f, nullptr, nullptr, bboxes);
     NLOS_CHECK_LAUNCH("preprocess_kernel(bboxes)");
     return 0;
 }

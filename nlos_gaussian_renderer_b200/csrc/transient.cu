@@ -146,7 +146,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                     const float v = Hw[kk * NLOS_TILE + pp];
                     if (v != 0.f && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
-                        atomicAdd(P.H + ((size_t)tile * NLOS_TILE + pp) * T + k, v * (s_hs[pp] * P.flush_scale) / (rk * rk + 1e-8f));
+                        atomicAdd(P.H + ((size_t)tile * NLOS_TILE + pp) * T + k, v * (s_hs[pp] * P.flush_scale) / (P.one_pass ? 1.0f : rk * rk + 1e-8f));
                     }
                 }
             };
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                     float v = 0.f;
                     if (k >= 0 && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
-                        v = P.gH[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (rk * rk + 1e-8f);
+                        v = P.gH[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (P.one_pass ? 1.0f : rk * rk + 1e-8f);
                     }
                     Hw[kk * NLOS_TILE + pp] = v;
                 }
@@ -609,7 +609,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         //                accuracy of GL3, <= 2.5e-5 of the peak, at the cost of GL2).  Passes: {A+, B+}, {A-, B-}
                                         //        kind 2: plain GL4 (s2 = 0).  Passes: {A+, B+}, {A-, B-} for each of the two node magnitudes.
                                         //      Without a second ray the two streams of a pass are the mirrored nodes {A+, A-} (half the passes).
-                                        const int kind = gpm <= TR_GPM_K0 ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);
+                                        const int kind = (P.one_pass || gpm <= TR_GPM_K0) ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);      // (one-pass entries: see analytic_filter_kernel)
                                         const bool two = ok0 && ok1;
                                         const float s2k = kind == 0 ? dt2 * (1.0f / 12.0f) : (kind == 1 ? dt2 * 0.018783611f : 0.f);
                                         float iu0, iu1;
@@ -869,8 +869,9 @@ extern "C" int nlosb200_debug_hit_dump(unsigned char* hits) { g_hit_dump = hits;
 static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                        const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls, int* work, float t0,
                        float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, int variant,
-                       const float* sh = nullptr, int sh_dim = 0, int sh_degree = 0)
+                       const float* sh = nullptr, int sh_dim = 0, int sh_degree = 0, int one_pass = 0)
 {
+    NLOS_REQUIRE(one_pass == 0 || (one_pass == 1 && mode == MODE_ANA), "transient: one_pass is a flag of the analytic-exact mode");
     NLOS_REQUIRE(sh_degree >= 0 && sh_degree <= 3, "transient: active_sh_degree=%d not in [0,3]", sh_degree);
     NLOS_REQUIRE(sh_degree == 0 || (sh && sh_dim >= (sh_degree + 1) * (sh_degree + 1)),
                  "transient: degree %d needs %d SH coefficients per Gaussian, features hold %d (the reference reads out of bounds here, volume_renderer.cu:110)",
@@ -880,7 +881,7 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
                  "transient: bad window/bucket/slice_len (bucket must be a power of two)");
     NLOS_REQUIRE(mode == MODE_NUM || mode == MODE_ANA, "transient: mode must be 0 (numerical) or 1 (analytic-exact)");
     NLOS_REQUIRE(variant == 0 || variant == 1, "transient: variant must be 0 (register accumulators) or 1 (direct to window)");
-    NLOS_REQUIRE(n_classes >= 1 && n_classes <= 2 && cls >= 0 && cls < n_classes, "transient: class %d of %d", cls, n_classes);
+    NLOS_REQUIRE(n_classes >= 1 && n_classes <= 4 && cls >= 0 && cls < n_classes, "transient: class %d of %d", cls, n_classes);
     NLOS_REQUIRE(tiles && records && list && list_bins && cell_offsets && work, "transient: null pointer");
     NLOS_REQUIRE(T <= 65535, "transient: T=%d > 65535", T);
     NLOS_REQUIRE(((uintptr_t)tiles % 16) == 0 && ((uintptr_t)records % 16) == 0, "transient: tiles/records must be 16-byte aligned");
@@ -892,7 +893,7 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
     P.cpt = n_classes * P.n_buckets; P.cell0 = cls * P.n_buckets;
     P.slice_len = slice_len; P.flush_scale = mode == MODE_NUM ? c_deltaT : 1.0f; P.mcut2 = mcut * mcut;
     P.H = nullptr; P.gH = nullptr; P.dacc = nullptr; P.counters = nullptr; P.hit_dump = g_hit_dump;
-    P.sh = sh; P.sh_dim = sh_dim; P.sh_degree = sh_degree; P.dsh = nullptr; P.part_stride = 0;
+    P.sh = sh; P.sh_dim = sh_dim; P.sh_degree = sh_degree; P.dsh = nullptr; P.part_stride = 0; P.one_pass = one_pass;
     return 0;
 }
 
@@ -901,11 +902,11 @@ extern "C" int nlosb200_transient_warps_per_block(void) { return TR_WPB; }
 extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                           const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                           int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                                          int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H, void* stream)
+                                          int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H, void* stream)
 {
     TransientParams P;
     int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
-                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree);
+                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree, one_pass);
     if (rc) return rc;
     NLOS_REQUIRE(H, "transient_forward: null H");
     cudaStream_t s = (cudaStream_t)stream;
@@ -922,12 +923,12 @@ extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A
 extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                            const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                            int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                                           int mode, int variant, int accumulate, const float* sh, int sh_dim, int sh_degree,
+                                           int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree,
                                            const float* grad_H, float* dacc, float* dsh, int per_tile_partials, void* stream)
 {
     TransientParams P;
     int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
-                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree);
+                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree, one_pass);
     if (rc) return rc;
     NLOS_REQUIRE(grad_H && dacc && (sh_degree == 0 || dsh), "transient_backward: null pointer");
     cudaStream_t s = (cudaStream_t)stream;
@@ -984,5 +985,40 @@ extern "C" int nlosb200_reduce_tile_partials(const float* partial, int n_tiles, 
     NLOS_REQUIRE(partial && out && n_tiles > 0 && n > 0, "reduce_tile_partials: bad arguments");
     reduce_tile_partials_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(partial, n_tiles, n, out);
     NLOS_CHECK_LAUNCH("reduce_tile_partials_kernel");
+    return 0;
+}
+
+// ---- one-pass analytic plan: rows of one-node bin integrals -> bin integrals.  A ray's Gaussian convolved with the unit box of a bin is, for rays
+// wider than 1.3 bins, the 1-node moment-matched mixture (variance + dt^2/12) up to a FIXED linear filter of the bin row,
+//     I = I1 - c4 d4(I1) - c6 d6(I1) ,   d2 = second central difference, c4 = 2.4e-4, c6 = -1.7e-4      (<= 1.6e-5 of the ray's peak;
+// tools/mix_filter_fit.py, tools/filter_plan_check.py).  The filter is the same for every ray, so it is applied ONCE to the summed rows of the
+// time-wide entries instead of a second recurrence pass per ray:
+//   forward : H[p,k] += w_k F(Ha[p,:])[k]        (Ha = unweighted rows of the one-pass launches, w_k = 1/(r_k^2+1e-8), cuda_autograd.py:308)
+//   backward: gHa[p,:] = F(w . gH[p,:])          (F is symmetric with zero padding; the one-pass entries keep 3 bins from both ends of the axis)
+#define FILT_C4 2.4e-4f
+#define FILT_C6 (-1.7e-4f)
+__global__ void __launch_bounds__(256) analytic_filter_kernel(const float* __restrict__ in, float* __restrict__ out, long long rows, int T, float t0, float dt,
+                                                              int backward)
+{
+    // 7-tap kernel of F: d4 = [1,-4,6,-4,1], d6 = [1,-6,15,-20,15,-6,1]
+    const float f0 = 1.0f - 6.0f * FILT_C4 + 20.0f * FILT_C6, f1 = 4.0f * FILT_C4 - 15.0f * FILT_C6, f2 = -FILT_C4 + 6.0f * FILT_C6, f3 = -FILT_C6;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * T) return;
+    const int k = (int)(i % T);
+    const float* row = in + (i - k);
+    auto w = [&](int kk) { const float r = fmaf((float)kk, dt, t0); return 1.0f / (r * r + 1e-8f); };
+    auto x = [&](int kk) { return (kk < 0 || kk >= T) ? 0.f : (backward ? row[kk] * w(kk) : row[kk]); };
+    const float y = f0 * x(k) + f1 * (x(k - 1) + x(k + 1)) + f2 * (x(k - 2) + x(k + 2)) + f3 * (x(k - 3) + x(k + 3));
+    if (backward) out[i] = y;
+    else out[i] += y * w(k);
+}
+
+// forward (backward = 0): out [rows,T] += w F(in) ; backward (1): out = F(w in)
+extern "C" int nlosb200_analytic_filter(const float* in, float* out, long long rows, int T, float t0, float dt, int backward, void* stream)
+{
+    NLOS_REQUIRE(in && out && rows > 0 && T > 0 && in != out, "analytic_filter: bad arguments");
+    const long long n = rows * T;
+    analytic_filter_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(in, out, rows, T, t0, dt, backward);
+    NLOS_CHECK_LAUNCH("analytic_filter_kernel");
     return 0;
 }

@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     const float v = Hw[kk * NLOS_TILE + pp];
                     if (v != 0.f && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
-                        atomicAdd(P.H + ((size_t)tile * NLOS_TILE + pp) * T + k, v * (s_hs[pp] * P.flush_scale) / (rk * rk + 1e-8f));
+                        atomicAdd(P.H + ((size_t)tile * NLOS_TILE + pp) * T + k, v * (s_hs[pp] * P.flush_scale) / (P.one_pass ? 1.0f : rk * rk + 1e-8f));
                     }
                 }
             };
@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     float v = 0.f;
                     if (k >= 0 && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
-                        v = P.gH[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (rk * rk + 1e-8f);
+                        v = P.gH[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (P.one_pass ? 1.0f : rk * rk + 1e-8f);
                     }
                     Hw[kk * NLOS_TILE + pp] = v;
                 }
@@ -627,7 +627,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                                     //                accuracy of GL3, <= 2.5e-5 of the peak, at the cost of GL2).  Passes: {A+, B+}, {A-, B-}
                                     //        kind 2: plain GL4 (s2 = 0).  Passes: {A+, B+}, {A-, B-} for each of the two node magnitudes.
                                     //      Without a second ray the two streams of a pass are the mirrored nodes {A+, A-} (half the passes).
-                                    const int kind = gpm <= TR_GPM_K0 ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);
+                                    const int kind = (P.one_pass || gpm <= TR_GPM_K0) ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);      // (one-pass entries: see analytic_filter_kernel)
                                     const bool two = ok0 && ok1;
                                     const float s2k = kind == 0 ? dt2 * (1.0f / 12.0f) : (kind == 1 ? dt2 * 0.018783611f : 0.f);
                                     float iu0, iu1;

@@ -42,6 +42,8 @@ struct TransientParams {
     int T, window, bucket, n_buckets, slice_len;
     float flush_scale;   // c*deltaT for the numerical mode (volume_renderer.cu:182), 1 for the analytic-exact mode
     float mcut2;
+    int one_pass;        // analytic mode, time-wide entries: every ray is a 1-node ray, H / gH are the UNWEIGHTED bin rows (no 1/(r^2+1e-8)):
+                         // the fixed 7-tap filter of analytic_filter_kernel and the radial weight are applied to the whole row outside
     float* H;            // forward out   [n_tiles*32, T]  (accumulated with REDs; caller zeroes)
     const float* gH;     // backward in   [n_tiles*32, T]
     float* dacc;         // backward out  [N, 16]          (accumulated with REDs; caller zeroes)

@@ -38,7 +38,7 @@ class _OccludedFn(torch.autograd.Function):
         records = _aligned(N * L.nlosb200_record_floats(), torch.float32, dev, 128)
         st = _lib.stream()
         _lib.call("nlosb200_preprocess", m.data_ptr(), ls.data_ptr(), rt.data_ptr(), op.data_ptr(), ft.data_ptr(), N, ft.shape[1], float(mod), 3.0,
-                  float(mcut), records.data_ptr(), None, None, st)
+                  float(mcut), 0.0, records.data_ptr(), None, None, st)
         n_rows = geom.n_tiles * TILE
         H = torch.zeros(n_rows, T, dtype=torch.float32, device=dev)
         t0 = float(ts[0])
@@ -64,7 +64,7 @@ class _OccludedFn(torch.autograd.Function):
         st = _lib.stream()
         records = _aligned(N * L.nlosb200_record_floats(), torch.float32, dev, 128)
         _lib.call("nlosb200_preprocess", m.data_ptr(), ls.data_ptr(), rt.data_ptr(), op.data_ptr(), ft.data_ptr(), N, ft.shape[1], mod, 3.0, mcut,
-                  records.data_ptr(), None, None, st)
+                  0.0, records.data_ptr(), None, None, st)
         g = geom.tile_grad(gH.to(torch.float32)).contiguous()
         dacc = torch.zeros(N, L.nlosb200_grad_floats(), dtype=torch.float32, device=dev)
         dsh = torch.zeros(N, 16, dtype=torch.float32, device=dev) if deg > 0 else None

@@ -34,7 +34,7 @@ class TransientRenderer:
 
     def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
                  mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=1.6, active_sh_degree=0,
-                 deterministic=False):
+                 deterministic=False, one_pass=True, one_pass_min_bins=1.3):
         """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
         (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries a warp pulls at a time from its
         tile's counter (default: 16..256, sized so that every warp of the persistent grid gets >= 32 slices).
@@ -65,7 +65,14 @@ class TransientRenderer:
         # into per-tile partial buffers [n_tiles, N, 16] that are summed in tile order.  Slower and memory-hungry: a debugging mode.
         self.deterministic = bool(deterministic)
         self.wpb = _lib.lib().nlosb200_transient_warps_per_block()
-        self.n_classes = 2 if self.variant == 2 else 1
+        # analytic mode, one-pass plan: entries of Gaussians whose smallest scale is >= one_pass_min_bins bins render every ray with ONE mixture
+        # node into a second buffer of unweighted rows; a fixed 7-tap filter (nlosb200_analytic_filter, <= 1.6e-5 of a ray's peak) turns those
+        # rows into bin integrals.  Halves the recurrence work of the 0.8 - 2.5 bin rays that otherwise take two nodes.
+        self.one_pass = bool(one_pass) and self.mode == 1
+        self.tw_min = float(one_pass_min_bins) * self.dt if self.one_pass else 0.0
+        self.n_fp = 2 if self.variant == 2 else 1
+        self.n_tw = 2 if self.one_pass else 1
+        self.n_classes = self.n_fp * self.n_tw
         self._N = None
         self._list = None
         self._pending = None           # (pinned header copy, event) of the previous prepare(): checked lazily, no host sync per step
@@ -110,7 +117,7 @@ class TransientRenderer:
     def _bin_args(self):
         g = self.geom
         return (g.tiles().data_ptr(), g.n_tiles, g.A, self.shell.data_ptr(), self._N, self.t0, self.dt, self.T, self.window, self.bucket,
-                self.n_classes)
+                self.n_classes, self.narrow_rays if self.n_fp == 2 else 0.0, self.mcut, int(self.n_tw == 2))
 
     def _check_pending(self):
         """Lazy overflow check of the PREVIOUS prepare(): its header copy finished long ago, so this does not stall the stream."""
@@ -151,17 +158,16 @@ class TransientRenderer:
         self.generation += 1
         st = _lib.stream()
         _lib.call("nlosb200_preprocess", means.data_ptr(), log_scales.data_ptr(), rotations.data_ptr(), opacities.data_ptr(),
-                  features.data_ptr(), N, features.shape[1], self.mod, self.sigma, self.mcut, self.records.data_ptr(),
+                  features.data_ptr(), N, features.shape[1], self.mod, self.sigma, self.mcut, self.tw_min, self.records.data_ptr(),
                   self.shell.data_ptr(), None, st)
-        _lib.call("nlosb200_bin_window_plan", *self._bin_args(), self.narrow_rays if self.variant == 2 else 0.0, self.mcut, self._slice, self.wpb,
+        _lib.call("nlosb200_bin_window_plan", *self._bin_args(), self._slice, self.wpb,
                   self.chunk_counts.data_ptr(), self.cell_counts.data_ptr(), self.cell_offsets.data_ptr(), self.tile_items.data_ptr(),
                   self.header.data_ptr(), st)
         if self._list is None:
             total = int(self.header.cpu()[0])                 # first call only: size the list buffer
             self.last_total = total
             self._grow(total)
-        _lib.call("nlosb200_bin_window_fill", *self._bin_args(), self.narrow_rays if self.variant == 2 else 0.0, self.mcut,
-                  self.chunk_counts.data_ptr(),
+        _lib.call("nlosb200_bin_window_fill", *self._bin_args(), self.chunk_counts.data_ptr(),
                   self.cell_offsets.data_ptr(), self._list.data_ptr(), self._list_bins.data_ptr(), self._list.numel(), self.header.data_ptr(), st)
         self.header_host.copy_(self.header, non_blocking=True)
         ev = torch.cuda.Event()
@@ -174,10 +180,14 @@ class TransientRenderer:
         return self.last_total
 
     def _launches(self):
-        """(cls, variant) of the render launches: one per entry class."""
-        if self.variant == 2:
-            return ((0, 1), (1, 0))           # class 0 = narrow entries -> direct-to-window kernel, class 1 = wide -> register accumulators
-        return ((0, self.variant),)
+        """(cls, variant, one_pass) of the render launches, one per entry class: class = footprint bit + n_fp * time-wide bit.  Footprint bit 0 =
+        narrow entries -> direct-to-window kernel, 1 = wide -> register accumulators; time-wide entries render one-pass."""
+        out = []
+        for tw in range(self.n_tw):
+            for fp in range(self.n_fp):
+                var = (1 if fp == 0 else 0) if self.n_fp == 2 else self.variant
+                out.append((fp + self.n_fp * tw, var, tw))
+        return tuple(out)
 
     def _render_args(self, cls):
         g = self.geom
@@ -192,9 +202,14 @@ class TransientRenderer:
     def forward_tiled(self):
         """-> H [n_tiles*32, T] in tile-major scan order (after prepare())."""
         H = torch.empty(self.geom.n_tiles * TILE, self.T, dtype=torch.float32, device=self.records.device)
-        for n, (cls, var) in enumerate(self._launches()):
-            _lib.call("nlosb200_transient_forward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, int(n > 0),
-                      *self._sh_args(), H.data_ptr(), _lib.stream())
+        Ha = torch.empty_like(H) if self.one_pass else None          # unweighted one-node rows of the time-wide entries
+        seen = [False, False]
+        for cls, var, op in self._launches():
+            _lib.call("nlosb200_transient_forward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, op, int(seen[op]),
+                      *self._sh_args(), (Ha if op else H).data_ptr(), _lib.stream())
+            seen[op] = True
+        if self.one_pass:
+            _lib.call("nlosb200_analytic_filter", Ha.data_ptr(), H.data_ptr(), H.shape[0], self.T, self.t0, self.dt, 0, _lib.stream())
         return H
 
     def forward(self, means, log_scales, rotations, opacities, features):
@@ -207,9 +222,14 @@ class TransientRenderer:
         det = self.deterministic
         dacc = self.dacc_part if det else self.dacc
         dsh = (self.dsh_part if det else self.dsh) if self._deg > 0 else None
-        for n, (cls, var) in enumerate(self._launches()):
-            _lib.call("nlosb200_transient_backward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, int(n > 0),
-                      *self._sh_args(), gH_tiled.data_ptr(), dacc.data_ptr(), dsh.data_ptr() if dsh is not None else None, int(det), _lib.stream())
+        gHa = None
+        if self.one_pass:                                            # weights of the one-pass launches: F(w gH)
+            gHa = torch.empty_like(gH_tiled)
+            _lib.call("nlosb200_analytic_filter", gH_tiled.data_ptr(), gHa.data_ptr(), gH_tiled.shape[0], self.T, self.t0, self.dt, 1, _lib.stream())
+        for n, (cls, var, op) in enumerate(self._launches()):
+            _lib.call("nlosb200_transient_backward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, op, int(n > 0),
+                      *self._sh_args(), (gHa if op else gH_tiled).data_ptr(), dacc.data_ptr(), dsh.data_ptr() if dsh is not None else None, int(det),
+                      _lib.stream())
         if det:
             _lib.call("nlosb200_reduce_tile_partials", dacc.data_ptr(), self.geom.n_tiles, self.dacc.numel(), self.dacc.data_ptr(), _lib.stream())
             if dsh is not None:

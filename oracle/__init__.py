@@ -195,12 +195,13 @@ ENTRY_SHIFT = 26      # list entry = gaussian id | (sub-interval index << 26)
 
 
 def entry_classes(scan_o, valid, lattice_step, Sy, Sx, tile_y, tile_x, means, log_scales, scaling_modifier, mcut, klo, khi, window, bucket,
-                  narrow_rays, exp_mode=1):
+                  narrow_rays, exp_mode=1, time_wide_min=0.0, T=None):
     """DEFINITION of the entry classes of the window binning (csrc/binning.cu header): class 0 ("narrow") when the Gaussian is listed once
     in the tile (khi - klo + 1 <= L) and  (6 / mcut) rad <= (narrow_rays * pitch) * sqrt(d2min)  in single-rounded fp32, with
     rad = mcut * max(scale), pitch = min over the tile's valid scan points of lattice_step (= min(dtheta, dphi), 0 where the lattice is
     unusable) and d2min = min over the tile's valid scan points of |mu - o|^2 (summed as ((dx^2 + dy^2) + dz^2)); else class 1.
-    scan_o [Sy*Sx,3], lattice_step [Sy*Sx] -> int32 [n_tiles, N]."""
+    narrow_rays = 0: no footprint classes (bit 0 everywhere).  time_wide_min > 0 adds the time-wide bit (class += n_fp): smallest scale >=
+    time_wide_min, listed once in the tile and klo >= 3, khi <= T - 4.  scan_o [Sy*Sx,3], lattice_step [Sy*Sx] -> int32 [n_tiles, N]."""
     f = np.float32
     scan_o, means, log_scales = _f(scan_o).reshape(Sy, Sx, 3), _f(means), _f(log_scales)
     step = _f(lattice_step).reshape(Sy, Sx)
@@ -221,22 +222,26 @@ def entry_classes(scan_o, valid, lattice_step, Sy, Sx, tile_y, tile_x, means, lo
             d2 = (d2 + (d[..., 2] * d[..., 2]).astype(f)).astype(f)
             rhs = ((f(narrow_rays) * st.min()).astype(f) * np.sqrt(d2.min(1)).astype(f)).astype(f)
             t = ty * ntx + tx
-            out[t] = np.where((khi[t] - klo[t] + 1 <= L) & (lhs <= rhs), 0, 1)
+            out[t] = np.where((khi[t] - klo[t] + 1 <= L) & (lhs <= rhs), 0, 1) if narrow_rays > 0 else 0
+    n_fp = 2 if narrow_rays > 0 else 1
+    if time_wide_min > 0:
+        tw = s.min(1) >= f(time_wide_min)
+        out = out + n_fp * (tw[None, :] & (klo >= 3) & (khi <= T - 4) & (khi - klo + 1 <= L)).astype(np.int32)
     return out
 
 
-def window_lists(klo, khi, T, window, bucket, cls=None):
+def window_lists(klo, khi, T, window, bucket, cls=None, n_classes=None):
     """DEFINITION of the window-binning lists the batched renderer consumes.  A Gaussian whose tile-level shell is
     [klo, khi] contributes entries e = 0 .. ceil(len/L)-1 with L = window - bucket; entry e covers bins
     [klo + e L, min(khi, klo + (e+1) L - 1)] and lives in cell (tile, (klo + e L) // bucket).  Per cell the entries are
     ascending in the Gaussian id.  With entry classes (cls int [n_tiles, N] of 0 / 1, entry_classes()) the cells of a tile are class-major:
-    cell = tile * 2 n_buckets + cls * n_buckets + bucket.  -> counts [cells] int32, offsets int64 [cells+1], list uint32."""
+    cell = tile * n_classes n_buckets + cls * n_buckets + bucket.  -> counts [cells] int32, offsets int64 [cells+1], list uint32."""
     klo = np.asarray(klo, np.int64)
     khi = np.asarray(khi, np.int64)
     nt, N = klo.shape
     L = window - bucket
     nb = -(-T // bucket)
-    ncls = 1 if cls is None else 2
+    ncls = 1 if cls is None else (2 if n_classes is None else int(n_classes))
     n_e = np.where(klo <= khi, -(-(khi - klo + 1) // L), 0)
     cells, vals = [], []
     for e in range(int(n_e.max()) if n_e.size else 0):

@@ -124,5 +124,5 @@ def test_error_convention_without_gpu():
     from nlos_gaussian_renderer_b200.transient import _f32c
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         _f32c(z)
-    rc = _lib.lib().nlosb200_bin_window_plan(None, 0, 0, None, 0, 0.0, 1.0, 0, 128, 8, 1, 0.0, 5.3, 0, 0, None, None, None, None, None, None)
+    rc = _lib.lib().nlosb200_bin_window_plan(None, 0, 0, None, 0, 0.0, 1.0, 0, 128, 8, 1, 0.0, 5.3, 0, 0, 0, None, None, None, None, None, None)
     assert rc < 0 and b"bad sizes" in _lib.lib().nlosb200_last_error()

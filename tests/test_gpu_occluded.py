@@ -22,7 +22,7 @@ def _gpu_lists(geom, params, cap):
     st = _lib.stream()
     m, ls, rt, op, ft = [p.contiguous() for p in params]
     _lib.call("nlosb200_preprocess", m.data_ptr(), ls.data_ptr(), rt.data_ptr(), op.reshape(-1).data_ptr(), ft.data_ptr(), N, ft.reshape(N, -1).shape[1], 1.0,
-              3.0, 5.3, rec.data_ptr(), None, None, st)
+              3.0, 5.3, 0.0, rec.data_ptr(), None, None, st)
     n_rows = geom.n_tiles * 32
     lists = torch.full((n_rows, geom.A * geom.A, cap + 1), -1, dtype=torch.int32, device="cuda")
     _lib.call("nlosb200_occluded_lists", geom.tiles().data_ptr(), geom.n_tiles, geom.A, rec.data_ptr(), N, cap, 0, n_rows, lists.data_ptr(), st)

@@ -33,8 +33,9 @@ def test_window_lists_bit_exact(shape, scale_mul, window, bucket):
     N, Sy, Sx, T, A = shape
     geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=scale_mul, device="cuda")
     seen = set()
-    for variant, narrow_rays in (("wide", 2.5), ("auto", 2.5), ("auto", 0.7), ("auto", 40.0)):
-        r = _renderer(geom, ta, "numerical", window=window, bucket=bucket, variant=variant, narrow_rays=narrow_rays)
+    for mode, variant, narrow_rays in (("numerical", "wide", 2.5), ("numerical", "auto", 2.5), ("numerical", "auto", 0.7), ("numerical", "auto", 40.0),
+                                       ("analytic", "auto", 2.5), ("analytic", "narrow", 2.5)):         # analytic: + the time-wide class bit (one-pass plan)
+        r = _renderer(geom, ta, mode, window=window, bucket=bucket, variant=variant, narrow_rays=narrow_rays)
         r.prepare(*params)
         cnt, off, lst = r.lists()
         (ocnt, ooff, olst), cls = util.oracle_window_lists(geom, ta, params, r)
@@ -42,8 +43,10 @@ def test_window_lists_bit_exact(shape, scale_mul, window, bucket):
         assert np.array_equal(off, ooff)
         assert np.array_equal(lst, olst)
         assert lst.size > 0
-        if cls is not None:
+        if cls is not None and mode == "numerical":
             seen.update(np.unique(cls).tolist())
+        if cls is not None and mode == "analytic" and window >= 96 and scale_mul == 1.0 and T >= 128:
+            assert (cls >= r.n_fp).any() and (cls < r.n_fp).any()      # time-wide and other entries both present
         if window == 32 and scale_mul > 1:
             assert (lst >> oracle.ENTRY_SHIFT).max() > 0          # split entries present
     if window >= 96 and scale_mul == 1.0:

@@ -55,15 +55,16 @@ def oracle_window_lists(geom, ta, params, r):
     klo, khi = oracle.shell_bins(np32(geom.scan_o), geom.Sy, geom.Sx, geom.tile_y, geom.tile_x, np32(params[0]), np32(params[1]),
                                  r.mod, r.mcut, ta["t0"], ta["dt"], T, exp_mode=1)
     cls = None
-    if r.n_classes == 2:
+    if r.n_classes > 1:
         lat = np32(geom.lattice)                         # (theta0, dtheta, phi0, dphi) of the linspaces
         A, PI = geom.A, np.float32(3.14159265358979)
         fast = (A > 1) & (lat[:, 1] > 1e-9) & (lat[:, 3] > 1e-9) & (lat[:, 0] >= 0) & (lat[:, 0] + lat[:, 1] * (A - 1) <= PI) & \
                (lat[:, 2] >= -PI) & (lat[:, 2] + lat[:, 3] * (A - 1) <= PI)             # csrc/preprocess.cu:build_scan_tiles_kernel `fast`
         step = np.where(fast, np.minimum(lat[:, 1], lat[:, 3]), np.float32(0)).astype(np.float32)
         cls = oracle.entry_classes(np32(geom.scan_o), None, step, geom.Sy, geom.Sx, geom.tile_y, geom.tile_x, np32(params[0]), np32(params[1]),
-                                   r.mod, r.mcut, klo, khi, r.window, r.bucket, r.narrow_rays, exp_mode=1)
-    return oracle.window_lists(klo, khi, T, r.window, r.bucket, cls), cls
+                                   r.mod, r.mcut, klo, khi, r.window, r.bucket, r.narrow_rays if r.n_fp == 2 else 0.0, exp_mode=1,
+                                   time_wide_min=r.tw_min, T=T)
+    return oracle.window_lists(klo, khi, T, r.window, r.bucket, cls, n_classes=r.n_classes), cls
 
 
 def hit_masks_gpu(r, params):
