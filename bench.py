@@ -42,8 +42,9 @@ def parse():
     ap.add_argument("--scaling", default="strong", choices=["weak", "strong"],
                     help="strong (default): the config's scan grid is dealt over the ranks; weak: every rank renders its own copy of the grid rows")
     ap.add_argument("--variant", default="auto", choices=["auto", "wide", "narrow"], help="scan-tile kernel per entry (TransientRenderer)")
-    ap.add_argument("--narrow-rays", type=float, default=1.6)
+    ap.add_argument("--narrow-rays", type=float, default=2.5)
     ap.add_argument("--contiguous", action="store_true", help="contiguous row slabs instead of round-robin tile rows")
+    ap.add_argument("--occlusion", action="store_true", help="add the `occlusion` block: the batched occlusion renderer (csrc/occluded.cu) on BASELINE configs[1]")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extra", action="store_true", help="skip the north_star / numerical_forward_only / grad_check blocks")
     ap.add_argument("--cpu-points", type=int, default=0, help="scan points in the CPU baseline sample (0 = auto)")
@@ -512,6 +513,32 @@ def run_b200(args):
             torch.cuda.empty_cache()
         line["north_star"] = {"workload": f"{Nn} Gaussians, {Syn}x{Sxn} confocal scan, {Tn} bins, A={An}: forward + backward kernels on ONE B200 (3 steps after 2 warm-ups)",
                               "frac_kind": "algorithmic-equivalent, as roofline.frac", **ns}
+    if world == 1 and args.occlusion:
+        # ---- the reference's per-ray occlusion semantics (256-per-ray lists in index order, shared transmittance) for a whole scan grid
+        from nlos_gaussian_renderer_b200.occluded import render_transient_batch_occluded
+        No, Syo, Sxo, To, Ao = scenes.CONFIGS["cfg2"]
+        go = ScanGeometry.wall_grid(Syo, Sxo, A=Ao)
+        go = ScanGeometry(go.scan_o.reshape(Syo, Sxo, 3), go.theta_range.reshape(Syo, Sxo, 2), go.phi_range.reshape(Syo, Sxo, 2), Ao, vp_y=go.vp_y, device=dev)
+        tao = scenes.time_axis(To)
+        po = [p.to(dev).requires_grad_() for p in scenes.make_gaussians(No, 1002)]
+        tso = tao["t_samples"].to(dev)
+        tf = tb = 0.0
+        for it in range(3):
+            e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            e[0].record()
+            Ho = render_transient_batch_occluded(go, tso, *po, tao["c"], tao["deltaT"])
+            e[1].record()
+            (Ho * Ho).sum().backward()
+            e[2].record()
+            torch.cuda.synchronize()
+            if it:
+                tf += e[0].elapsed_time(e[1]) / 2; tb += e[1].elapsed_time(e[2]) / 2
+        line["occlusion"] = {"workload": f"cfg2 with occlusion: {No} Gaussians, {Syo}x{Sxo} scan, {To} bins, A={Ao}, 256-per-ray lists (the reference's cap binds on "
+                                         "most rays at this size), numerical integration", "fwd_ms": tf, "bwd_ms": tb,
+                             "fwd_includes": "preprocess + per-ray list building + render; bwd: lists + recompute + gradients (nothing of size [rays, T] is stored)",
+                             "rays": Syo * Sxo * Ao * Ao, "ray_gaussian_pairs_max": Syo * Sxo * Ao * Ao * 256}
+        del Ho, po
+        torch.cuda.empty_cache()
     if world == 1 and not args.no_cpu_baseline:
         b = cpu_baseline(args.config, args.cpu_points)
         line["cpu_baseline"] = {k: b[k] for k in ("value", "unit", "cores", "kind", "sample")}

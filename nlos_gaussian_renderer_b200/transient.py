@@ -33,7 +33,7 @@ class TransientRenderer:
     """Stateful renderer for one ScanGeometry: owns the preprocess / binning workspaces."""
 
     def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
-                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=1.6, active_sh_degree=0,
+                 mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=2.5, active_sh_degree=0,
                  deterministic=False, one_pass=True, one_pass_min_bins=1.3):
         """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
         (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries a warp pulls at a time from its
