@@ -111,24 +111,36 @@ def workload_name(cfg, shape, world, mode, scaling):
 
 
 def ncu_traffic(cfg, mode):
-    """(bytes, tag): dram__bytes_read.sum + dram__bytes_write.sum of the backward kernel per launch, from the newest COMMITTED `ncu --set full`
-    capture of this workload (profiles/rNN_x_ncu_raw_<cfg>_<mode>.txt).  It is not a measurement of this run: the tag says which capture."""
+    """(bytes, tag): dram__bytes_read.sum + dram__bytes_write.sum of the dominant BACKWARD kernel launch (the longest one), from the newest
+    COMMITTED `ncu --set full` capture of this workload (profiles/rNN_x_ncu_raw_<cfg>_<mode>.txt, written by tools/ncu_summary.py raw).
+    It is not a measurement of this run: the tag says which capture."""
     import glob
     found = sorted(glob.glob(os.path.join(ROOT, "profiles", f"r[0-9][0-9]_?_ncu_raw_{cfg}_{mode}.txt")))
     if not found:
         return None, None
     path = found[-1]
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
-    tot = 0.0
+    names, dur, rd, wr = [], [], [], []
+    num = lambda c: float(c) if c.strip().replace(".", "", 1).replace("e+", "", 1).replace("e-", "", 1).isdigit() else float("nan")
     for ln in open(path):
-        if ln.startswith("dram__bytes_read.sum") or ln.startswith("dram__bytes_write.sum"):
-            u = ln.split("[")[1].split("]")[0]
-            cols = [c.strip() for c in ln.split("|")[1:]]
-            try:
-                tot += float(cols[-1]) * unit.get(u, 1.0)            # last column = the backward kernel
-            except ValueError:
-                pass
-    return (tot or None), os.path.basename(path)
+        cols = [c.strip() for c in ln.rstrip("\n").split("|")]
+        if ln.startswith("metric |"):
+            names = cols[1:]
+        elif ln.startswith("gpu__time_duration.sum"):
+            dur = [num(c) for c in cols[1:]]
+        elif ln.startswith("dram__bytes_read.sum") or ln.startswith("dram__bytes_write.sum"):
+            u = unit.get(ln.split("[")[1].split("]")[0], 1.0)
+            vals = [num(c) * u for c in cols[1:]]
+            if ln.startswith("dram__bytes_read"):
+                rd = vals
+            else:
+                wr = vals
+    best, tot = -1.0, None
+    for i, n in enumerate(names):
+        is_bwd = ", 1, " in n or ", 1>" in n                 # transient[_narrow]_kernel<MODE, BWD = 1, SH>
+        if is_bwd and i < len(dur) and i < len(rd) and i < len(wr) and dur[i] == dur[i] and rd[i] == rd[i] and dur[i] > best:
+            best, tot = dur[i], rd[i] + (wr[i] if wr[i] == wr[i] else 0.0)
+    return tot, os.path.basename(path)
 
 
 # ----------------------------------------------------------------------------------------------------------------

@@ -34,7 +34,7 @@ class TransientRenderer:
 
     def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
                  mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=2.5, active_sh_degree=0,
-                 deterministic=False, one_pass=True, one_pass_min_bins=1.3):
+                 deterministic=False, one_pass=None, one_pass_min_bins=1.3):
         """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
         (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries a warp pulls at a time from its
         tile's counter (default: 16..256, sized so that every warp of the persistent grid gets >= 32 slices).
@@ -68,6 +68,10 @@ class TransientRenderer:
         # analytic mode, one-pass plan: entries of Gaussians whose smallest scale is >= one_pass_min_bins bins render every ray with ONE mixture
         # node into a second buffer of unweighted rows; a fixed 7-tap filter (nlosb200_analytic_filter, <= 1.6e-5 of a ray's peak) turns those
         # rows into bin integrals.  Halves the recurrence work of the 0.8 - 2.5 bin rays that otherwise take two nodes.
+        # (one_pass=None: on for the analytic mode unless the scan grid is tiny -- the plan costs two more launches per pass, which is what a
+        #  launch-bound scene like BASELINE configs[0] (8 tiles, 1.4 ms per step) would then be made of)
+        if one_pass is None:
+            one_pass = geom.n_tiles >= 64
         self.one_pass = bool(one_pass) and self.mode == 1
         self.tw_min = float(one_pass_min_bins) * self.dt if self.one_pass else 0.0
         self.n_fp = 2 if self.variant == 2 else 1
