@@ -456,7 +456,8 @@ def run_b200(args):
         if traffic:
             hbm_view.update({"achieved": traffic / (bwd_ms * 1e-3) / 1e9, "frac": traffic / (bwd_ms * 1e-3) / 1e9 / hbm_peak, "bytes_per_launch": traffic})
         n_bytes = N * 12 * 4
-        n_cls = rnd.n_classes
+        n_cls = len(rnd._launch_groups())        # one launch per kernel variant (its entry classes are segments of the launch)
+        n_flt = 1 if rnd.one_pass else 0
         line = {
             "metric": METRIC, "value": Wb / (ms_step * 1e-3), "unit": "Gaussian-bin evals/s",
             "n_gpus": world, "steps": args.steps, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True,
@@ -471,8 +472,9 @@ def run_b200(args):
             "clocks": clocks,
             "e2e": {"value": Wb / (ms_e2e / args.steps * 1e-3), "unit": "Gaussian-bin evals/s", "h2d_bytes_per_step": n_bytes,
                     "d2h_bytes_per_step": n_bytes + 4, "ms_per_step": ms_e2e / args.steps},
-            "gpu_launches": (1 + 4 + n_cls + 1 + n_cls + 1) * args.steps,
-            "gpu_launches_per_step": {"preprocess": 1, "binning": 4, "transient_forward": n_cls, "loss": 1, "transient_backward": n_cls, "chain": 1},
+            "gpu_launches": (1 + 4 + n_cls + n_flt + 1 + n_flt + n_cls + 1) * args.steps,
+            "gpu_launches_per_step": {"preprocess": 1, "binning": 4, "transient_forward": n_cls, "analytic_filter": 2 * n_flt, "loss": 1, "transient_backward": n_cls,
+                                      "chain": 1, "entry_classes": rnd.n_classes},
             "roofline": {"bound": "compute (" + rb["binding_pipe"] + " pipe)", "kernel": f"transient kernels <{args.mode},bwd> ({args.variant})",
                          "achieved": rb["achieved"], "peak": rb["peak"], "unit": "TFLOP/s", "frac": rb["frac"],
                          "frac_kind": "algorithmic-equivalent (SURVEY 8d: W_s x the algorithmic flop of one sample-eval / launch time / pipe peak); "

@@ -83,8 +83,10 @@ int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float
  * nothing: the overflow flag of bin_window_fill tells).  The cells of a tile are class-major: n_classes * n_buckets per tile, a launch
  * walks class `cls` (nlosb200_bin_window_plan).  variant 0 = register-accumulator kernel (wide footprints, transient.cu), 1 = direct-to-window
  * kernel (footprints of a few rays, transient_narrow.cu); both render any entry, they differ in speed only.  accumulate = 0: H / dacc /
- * counters are zeroed by the callee first; 1: the launch adds to them (second class).  `work` is int32 scratch [n_tiles] (zeroed by the
- * callee): the per-tile slice counters the persistent CTAs pull work from; slice_len = list entries a warp takes at a time.
+ * counters are zeroed by the callee first; 1: the launch adds to them (further classes).  A launch may walk a SECOND class in the same grid
+ * (cls2 >= 0, else -1) with its own one_pass flag and output rows H2 / input rows grad_H2 (may equal H / grad_H): the persistent CTAs steal
+ * from both classes' lists, so nothing idles between them.  `work` is int32 scratch [2*n_tiles] (zeroed by the callee): the per-(class, tile)
+ * slice counters the persistent CTAs pull work from; slice_len = list entries a warp takes at a time.
  * View-dependent albedo: sh_degree 1..3 with sh = the raw SH coefficients [N, sh_dim], sh_dim >= (sh_degree+1)^2 (fewer is an error: the
  * reference reads out of bounds, volume_renderer.cu:110): albedo(g, p) = max(SH(dir(mu_g - o_p)) + 0.5, 0) per (Gaussian, scan point)
  * (volume_renderer.cu:107-111, spherical_harmonics.cuh:20-80); the backward then also fills dsh [N,16] = dL/d(SH coefficients) and adds the
@@ -92,12 +94,14 @@ int nlosb200_bin_window_fill(const float* tiles, int n_tiles, int A, const float
 int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                               int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H, void* stream);
+                               int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H,
+                               int cls2, int one_pass2, float* H2, void* stream);
 int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                 const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                 int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
                                 int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree,
-                                const float* grad_H, float* dacc, float* dsh, int per_tile_partials, void* stream);
+                                const float* grad_H, int cls2, int one_pass2, const float* grad_H2, float* dacc, float* dsh,
+                                int per_tile_partials, void* stream);
 /* One-pass analytic plan (mode 1, launches over the TIME-WIDE entry classes of the binning: smallest scale >= 1.3 bins): one_pass = 1 renders
  * every ray with the 1-node mixture and leaves the 1/(r^2+1e-8) weight out -- H is then a buffer Ha of unweighted rows, and
  *   forward : nlosb200_analytic_filter(Ha, H, rows, T, t0, dt, 0)   adds  w F(Ha)  to H   (F = the fixed 7-tap filter that turns 1-node rows into

@@ -75,24 +75,27 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
     unsigned tphase = 0;
     // ---- persistent CTA: walk the tiles cyclically from an evenly spread start; warps pull slices of the current tile's
     //      entry list from its global counter, so CTAs that run out of work join the tiles that still have some
-    int t_cur = (int)(((long long)blockIdx.x * P.n_tiles) / gridDim.x), visited = 0;
+    const int n_vt = P.n_tiles * P.n_seg;          // virtual tiles (segment, tile): one launch walks up to two entry classes
+    int t_cur = (int)(((long long)blockIdx.x * n_vt) / gridDim.x), visited = 0;
     for (;;) {
         if (warp == 0) {
             int found = -1, adv = 0;
-            while (visited + adv < P.n_tiles) {
+            while (visited + adv < n_vt) {
                 const int off = adv + lane;
                 bool has = false;
-                if (visited + off < P.n_tiles) {
+                if (visited + off < n_vt) {
                     int t = t_cur + off;
-                    if (t >= P.n_tiles) t -= P.n_tiles;
-                    const long long tot = P.cell_offsets[(size_t)t * P.cpt + P.cell0 + P.n_buckets] - P.cell_offsets[(size_t)t * P.cpt + P.cell0];
+                    if (t >= n_vt) t -= n_vt;
+                    const int sg = P.n_seg == 2 ? (t & 1) : 0, tt = P.n_seg == 2 ? (t >> 1) : t;
+                    const long long* co = P.cell_offsets + (size_t)tt * P.cpt + P.seg_cell0[sg];
+                    const long long tot = co[P.n_buckets] - co[0];
                     has = *(volatile int*)(P.work + t) < (int)((tot + P.slice_len - 1) / P.slice_len);
                 }
                 const unsigned m = __ballot_sync(0xffffffffu, has);
                 if (m) {
                     const int f = __ffs(m) - 1;
                     found = t_cur + adv + f;
-                    if (found >= P.n_tiles) found -= P.n_tiles;
+                    if (found >= n_vt) found -= n_vt;
                     adv += f + 1;
                     break;
                 }
@@ -101,18 +104,23 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
             if (lane == 0) { s_ctl[0] = found; s_ctl[1] = adv; }
         }
         __syncthreads();
-        const int tile = s_ctl[0];
-        if (tile < 0) break;
+        const int vt = s_ctl[0];
+        if (vt < 0) break;
+        const int seg = P.n_seg == 2 ? (vt & 1) : 0, tile = P.n_seg == 2 ? (vt >> 1) : vt;      // segments interleaved: a CTA's share of the ring holds both classes of its tiles
+        const int seg_cell0 = P.seg_cell0[seg];
+        const bool one_pass = P.seg_one_pass[seg] != 0;
+        float* const Hout = P.seg_H[seg];
+        const float* const gHin = P.seg_gH[seg];
         visited += s_ctl[1];
         t_cur += s_ctl[1];
-        if (t_cur >= P.n_tiles) t_cur -= P.n_tiles;
+        if (t_cur >= n_vt) t_cur -= n_vt;
         if (threadIdx.x == 0) {
             fence_proxy_async();
             mbar_arrive_expect_tx(&s_bar[0], (uint32_t)tile_floats * 4u);
             bulk_g2s(s_tab, P.tiles + (size_t)tile * tile_floats, (uint32_t)tile_floats * 4u, &s_bar[0]);
         }
-        const long long tile_beg = P.cell_offsets[(size_t)tile * P.cpt + P.cell0];
-        const long long tile_tot = P.cell_offsets[(size_t)tile * P.cpt + P.cell0 + P.n_buckets] - tile_beg;
+        const long long tile_beg = P.cell_offsets[(size_t)tile * P.cpt + seg_cell0];
+        const long long tile_tot = P.cell_offsets[(size_t)tile * P.cpt + seg_cell0 + P.n_buckets] - tile_beg;
         const int n_slices = (int)((tile_tot + P.slice_len - 1) / P.slice_len);
         mbar_wait(&s_bar[0], tphase);   // lattice tables + scan-point info have landed
         tphase ^= 1u;
@@ -125,7 +133,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
 
         for (;;) {
             int sl = 0;
-            if (lane == 0) sl = atomicAdd(P.work + tile, 1);
+            if (lane == 0) sl = atomicAdd(P.work + vt, 1);
             sl = __shfl_sync(0xffffffffu, sl, 0);
             if (sl >= n_slices) break;
             const long long first = (long long)sl * P.slice_len;
@@ -146,7 +154,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                     const float v = Hw[kk * NLOS_TILE + pp];
                     if (v != 0.f && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
-                        atomicAdd(P.H + ((size_t)tile * NLOS_TILE + pp) * T + k, v * (s_hs[pp] * P.flush_scale) / (P.one_pass ? 1.0f : rk * rk + 1e-8f));
+                        atomicAdd(Hout + ((size_t)tile * NLOS_TILE + pp) * T + k, v * (s_hs[pp] * P.flush_scale) / (one_pass ? 1.0f : rk * rk + 1e-8f));
                     }
                 }
             };
@@ -157,7 +165,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                     float v = 0.f;
                     if (k >= 0 && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
-                        v = P.gH[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (P.one_pass ? 1.0f : rk * rk + 1e-8f);
+                        v = gHin[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (one_pass ? 1.0f : rk * rk + 1e-8f);
                     }
                     Hw[kk * NLOS_TILE + pp] = v;
                 }
@@ -609,7 +617,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                                         //                accuracy of GL3, <= 2.5e-5 of the peak, at the cost of GL2).  Passes: {A+, B+}, {A-, B-}
                                         //        kind 2: plain GL4 (s2 = 0).  Passes: {A+, B+}, {A-, B-} for each of the two node magnitudes.
                                         //      Without a second ray the two streams of a pass are the mirrored nodes {A+, A-} (half the passes).
-                                        const int kind = (P.one_pass || gpm <= TR_GPM_K0) ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);      // (one-pass entries: see analytic_filter_kernel)
+                                        const int kind = (one_pass || gpm <= TR_GPM_K0) ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);      // (one-pass entries: see analytic_filter_kernel)
                                         const bool two = ok0 && ok1;
                                         const float s2k = kind == 0 ? dt2 * (1.0f / 12.0f) : (kind == 1 ? dt2 * 0.018783611f : 0.f);
                                         float iu0, iu1;
@@ -850,7 +858,7 @@ static int launch_transient(const TransientParams& P, cudaStream_t s, const char
 {
     if (!SH && P.sh_degree > 0 && MODE != MODE_COUNT) return launch_transient<MODE, BWD, MODE != MODE_COUNT>(P, s, name);     // view-dependent albedo: its own instantiation
     int n_sm = transient_num_sms();
-    cudaError_t em = cudaMemsetAsync(P.work, 0, (size_t)P.n_tiles * sizeof(int), s);
+    cudaError_t em = cudaMemsetAsync(P.work, 0, (size_t)P.n_tiles * P.n_seg * sizeof(int), s);
     NLOS_REQUIRE(em == cudaSuccess, "%s: memset: %s", name, cudaGetErrorString(em));
     size_t smem = transient_smem_bytes(P.A, P.window);
     NLOS_REQUIRE(smem <= 227 * 1024, "%s: %zu B of shared memory needed (A=%d, window=%d) > 227 KB", name, smem, P.A, P.window);
@@ -869,9 +877,11 @@ extern "C" int nlosb200_debug_hit_dump(unsigned char* hits) { g_hit_dump = hits;
 static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                        const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls, int* work, float t0,
                        float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut, int mode, int variant,
-                       const float* sh = nullptr, int sh_dim = 0, int sh_degree = 0, int one_pass = 0)
+                       const float* sh = nullptr, int sh_dim = 0, int sh_degree = 0, int one_pass = 0, int cls2 = -1, int one_pass2 = 0)
 {
-    NLOS_REQUIRE(one_pass == 0 || (one_pass == 1 && mode == MODE_ANA), "transient: one_pass is a flag of the analytic-exact mode");
+    NLOS_REQUIRE((one_pass == 0 || (one_pass == 1 && mode == MODE_ANA)) && (one_pass2 == 0 || (one_pass2 == 1 && mode == MODE_ANA)),
+                 "transient: one_pass is a flag of the analytic-exact mode");
+    NLOS_REQUIRE(cls2 >= -1 && cls2 < n_classes && cls2 != cls, "transient: second class %d of %d (first %d)", cls2, n_classes, cls);
     NLOS_REQUIRE(sh_degree >= 0 && sh_degree <= 3, "transient: active_sh_degree=%d not in [0,3]", sh_degree);
     NLOS_REQUIRE(sh_degree == 0 || (sh && sh_dim >= (sh_degree + 1) * (sh_degree + 1)),
                  "transient: degree %d needs %d SH coefficients per Gaussian, features hold %d (the reference reads out of bounds here, volume_renderer.cu:110)",
@@ -890,10 +900,12 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
     P.list_capacity = list_capacity;
     P.cell_offsets = cell_offsets; P.work = work;
     P.t0 = t0; P.dt = dt; P.inv_dt = 1.0f / dt; P.T = T; P.window = window; P.bucket = bucket; P.n_buckets = (T + bucket - 1) / bucket;
-    P.cpt = n_classes * P.n_buckets; P.cell0 = cls * P.n_buckets;
+    P.cpt = n_classes * P.n_buckets;
+    P.n_seg = cls2 >= 0 ? 2 : 1; P.seg_cell0[0] = cls * P.n_buckets; P.seg_cell0[1] = (cls2 >= 0 ? cls2 : cls) * P.n_buckets;
+    P.seg_one_pass[0] = one_pass; P.seg_one_pass[1] = one_pass2;
     P.slice_len = slice_len; P.flush_scale = mode == MODE_NUM ? c_deltaT : 1.0f; P.mcut2 = mcut * mcut;
-    P.H = nullptr; P.gH = nullptr; P.dacc = nullptr; P.counters = nullptr; P.hit_dump = g_hit_dump;
-    P.sh = sh; P.sh_dim = sh_dim; P.sh_degree = sh_degree; P.dsh = nullptr; P.part_stride = 0; P.one_pass = one_pass;
+    P.seg_H[0] = P.seg_H[1] = nullptr; P.seg_gH[0] = P.seg_gH[1] = nullptr; P.dacc = nullptr; P.counters = nullptr; P.hit_dump = g_hit_dump;
+    P.sh = sh; P.sh_dim = sh_dim; P.sh_degree = sh_degree; P.dsh = nullptr; P.part_stride = 0;
     return 0;
 }
 
@@ -902,19 +914,21 @@ extern "C" int nlosb200_transient_warps_per_block(void) { return TR_WPB; }
 extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                           const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                           int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
-                                          int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H, void* stream)
+                                          int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H,
+                                          int cls2, int one_pass2, float* H2, void* stream)
 {
     TransientParams P;
     int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
-                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree, one_pass);
+                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree, one_pass, cls2, one_pass2);
     if (rc) return rc;
-    NLOS_REQUIRE(H, "transient_forward: null H");
+    NLOS_REQUIRE(H && (cls2 < 0 || H2), "transient_forward: null H");
     cudaStream_t s = (cudaStream_t)stream;
     if (!accumulate) {
         cudaError_t e = cudaMemsetAsync(H, 0, (size_t)n_tiles * NLOS_TILE * T * sizeof(float), s);
+        if (e == cudaSuccess && cls2 >= 0 && H2 != H) e = cudaMemsetAsync(H2, 0, (size_t)n_tiles * NLOS_TILE * T * sizeof(float), s);
         NLOS_REQUIRE(e == cudaSuccess, "transient_forward: memset: %s", cudaGetErrorString(e));
     }
-    P.H = H;
+    P.seg_H[0] = H; P.seg_H[1] = cls2 >= 0 ? H2 : H;
     if (variant == 1) return launch_transient_narrow(P, mode, false, s);
     return mode == MODE_NUM ? launch_transient<MODE_NUM, false>(P, s, "transient_kernel<num,fwd>")
                             : launch_transient<MODE_ANA, false>(P, s, "transient_kernel<ana,fwd>");
@@ -924,13 +938,15 @@ extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int 
                                            const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                            int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
                                            int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree,
-                                           const float* grad_H, float* dacc, float* dsh, int per_tile_partials, void* stream)
+                                           const float* grad_H, int cls2, int one_pass2, const float* grad_H2, float* dacc, float* dsh,
+                                           int per_tile_partials, void* stream)
 {
     TransientParams P;
     int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
-                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree, one_pass);
+                         bucket, slice_len, c_deltaT, mcut, mode, variant, sh, sh_dim, sh_degree, one_pass, cls2, one_pass2);
     if (rc) return rc;
-    NLOS_REQUIRE(grad_H && dacc && (sh_degree == 0 || dsh), "transient_backward: null pointer");
+    NLOS_REQUIRE(grad_H && (cls2 < 0 || grad_H2) && dacc && (sh_degree == 0 || dsh), "transient_backward: null pointer");
+    NLOS_REQUIRE(!(per_tile_partials && cls2 >= 0), "transient_backward: per-tile partials (deterministic mode) take one class per launch");
     cudaStream_t s = (cudaStream_t)stream;
     const size_t n_part = per_tile_partials ? (size_t)n_tiles : 1;
     if (!accumulate) {
@@ -941,7 +957,7 @@ extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int 
             NLOS_REQUIRE(e == cudaSuccess, "transient_backward: memset: %s", cudaGetErrorString(e));
         }
     }
-    P.gH = grad_H;
+    P.seg_gH[0] = grad_H; P.seg_gH[1] = cls2 >= 0 ? grad_H2 : grad_H;
     P.dacc = dacc;
     P.dsh = dsh;
     P.part_stride = per_tile_partials ? (size_t)N * NLOS_GRAD_FLOATS : 0;

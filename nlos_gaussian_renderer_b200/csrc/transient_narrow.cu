@@ -51,24 +51,27 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
     unsigned tphase = 0;
     // ---- persistent CTA: walk the tiles cyclically from an evenly spread start; warps pull slices of the current tile's
     //      entry list from its global counter, so CTAs that run out of work join the tiles that still have some
-    int t_cur = (int)(((long long)blockIdx.x * P.n_tiles) / gridDim.x), visited = 0;
+    const int n_vt = P.n_tiles * P.n_seg;          // virtual tiles (segment, tile): one launch walks up to two entry classes
+    int t_cur = (int)(((long long)blockIdx.x * n_vt) / gridDim.x), visited = 0;
     for (;;) {
         if (warp == 0) {
             int found = -1, adv = 0;
-            while (visited + adv < P.n_tiles) {
+            while (visited + adv < n_vt) {
                 const int off = adv + lane;
                 bool has = false;
-                if (visited + off < P.n_tiles) {
+                if (visited + off < n_vt) {
                     int t = t_cur + off;
-                    if (t >= P.n_tiles) t -= P.n_tiles;
-                    const long long tot = P.cell_offsets[(size_t)t * P.cpt + P.cell0 + P.n_buckets] - P.cell_offsets[(size_t)t * P.cpt + P.cell0];
+                    if (t >= n_vt) t -= n_vt;
+                    const int sg = P.n_seg == 2 ? (t & 1) : 0, tt = P.n_seg == 2 ? (t >> 1) : t;
+                    const long long* co = P.cell_offsets + (size_t)tt * P.cpt + P.seg_cell0[sg];
+                    const long long tot = co[P.n_buckets] - co[0];
                     has = *(volatile int*)(P.work + t) < (int)((tot + P.slice_len - 1) / P.slice_len);
                 }
                 const unsigned m = __ballot_sync(0xffffffffu, has);
                 if (m) {
                     const int f = __ffs(m) - 1;
                     found = t_cur + adv + f;
-                    if (found >= P.n_tiles) found -= P.n_tiles;
+                    if (found >= n_vt) found -= n_vt;
                     adv += f + 1;
                     break;
                 }
@@ -77,18 +80,23 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
             if (lane == 0) { s_ctl[0] = found; s_ctl[1] = adv; }
         }
         __syncthreads();
-        const int tile = s_ctl[0];
-        if (tile < 0) break;
+        const int vt = s_ctl[0];
+        if (vt < 0) break;
+        const int seg = P.n_seg == 2 ? (vt & 1) : 0, tile = P.n_seg == 2 ? (vt >> 1) : vt;      // segments interleaved: a CTA's share of the ring holds both classes of its tiles
+        const int seg_cell0 = P.seg_cell0[seg];
+        const bool one_pass = P.seg_one_pass[seg] != 0;
+        float* const Hout = P.seg_H[seg];
+        const float* const gHin = P.seg_gH[seg];
         visited += s_ctl[1];
         t_cur += s_ctl[1];
-        if (t_cur >= P.n_tiles) t_cur -= P.n_tiles;
+        if (t_cur >= n_vt) t_cur -= n_vt;
         if (threadIdx.x == 0) {
             fence_proxy_async();
             mbar_arrive_expect_tx(&s_bar[0], (uint32_t)tile_floats * 4u);
             bulk_g2s(s_tab, P.tiles + (size_t)tile * tile_floats, (uint32_t)tile_floats * 4u, &s_bar[0]);
         }
-        const long long tile_beg = P.cell_offsets[(size_t)tile * P.cpt + P.cell0];
-        const long long tile_tot = P.cell_offsets[(size_t)tile * P.cpt + P.cell0 + P.n_buckets] - tile_beg;
+        const long long tile_beg = P.cell_offsets[(size_t)tile * P.cpt + seg_cell0];
+        const long long tile_tot = P.cell_offsets[(size_t)tile * P.cpt + seg_cell0 + P.n_buckets] - tile_beg;
         const int n_slices = (int)((tile_tot + P.slice_len - 1) / P.slice_len);
         mbar_wait(&s_bar[0], tphase);   // lattice tables + scan-point info have landed
         tphase ^= 1u;
@@ -100,7 +108,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
 
         for (;;) {
             int sl = 0;
-            if (lane == 0) sl = atomicAdd(P.work + tile, 1);
+            if (lane == 0) sl = atomicAdd(P.work + vt, 1);
             sl = __shfl_sync(0xffffffffu, sl, 0);
             if (sl >= n_slices) break;
             const long long first = (long long)sl * P.slice_len;
@@ -121,7 +129,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     const float v = Hw[kk * NLOS_TILE + pp];
                     if (v != 0.f && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
-                        atomicAdd(P.H + ((size_t)tile * NLOS_TILE + pp) * T + k, v * (s_hs[pp] * P.flush_scale) / (P.one_pass ? 1.0f : rk * rk + 1e-8f));
+                        atomicAdd(Hout + ((size_t)tile * NLOS_TILE + pp) * T + k, v * (s_hs[pp] * P.flush_scale) / (one_pass ? 1.0f : rk * rk + 1e-8f));
                     }
                 }
             };
@@ -132,7 +140,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     float v = 0.f;
                     if (k >= 0 && k < T) {
                         const float rk = fmaf((float)k, dt, t0);
-                        v = P.gH[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (P.one_pass ? 1.0f : rk * rk + 1e-8f);
+                        v = gHin[((size_t)tile * NLOS_TILE + pp) * T + k] * (s_hs[pp] * P.flush_scale) / (one_pass ? 1.0f : rk * rk + 1e-8f);
                     }
                     Hw[kk * NLOS_TILE + pp] = v;
                 }
@@ -627,7 +635,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                                     //                accuracy of GL3, <= 2.5e-5 of the peak, at the cost of GL2).  Passes: {A+, B+}, {A-, B-}
                                     //        kind 2: plain GL4 (s2 = 0).  Passes: {A+, B+}, {A-, B-} for each of the two node magnitudes.
                                     //      Without a second ray the two streams of a pass are the mirrored nodes {A+, A-} (half the passes).
-                                    const int kind = (P.one_pass || gpm <= TR_GPM_K0) ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);      // (one-pass entries: see analytic_filter_kernel)
+                                    const int kind = (one_pass || gpm <= TR_GPM_K0) ? 0 : (gpm <= TR_GPM_K1 ? 1 : 2);      // (one-pass entries: see analytic_filter_kernel)
                                     const bool two = ok0 && ok1;
                                     const float s2k = kind == 0 ? dt2 * (1.0f / 12.0f) : (kind == 1 ? dt2 * 0.018783611f : 0.f);
                                     float iu0, iu1;
@@ -822,7 +830,7 @@ static int launch_narrow(const TransientParams& P, cudaStream_t s, const char* n
 {
     if (!SH && P.sh_degree > 0) return launch_narrow<MODE, BWD, true>(P, s, name);     // view-dependent albedo: its own instantiation
     int n_sm = transient_num_sms();
-    cudaError_t em = cudaMemsetAsync(P.work, 0, (size_t)P.n_tiles * sizeof(int), s);
+    cudaError_t em = cudaMemsetAsync(P.work, 0, (size_t)P.n_tiles * P.n_seg * sizeof(int), s);
     NLOS_REQUIRE(em == cudaSuccess, "%s: memset: %s", name, cudaGetErrorString(em));
     size_t smem = transient_smem_bytes(P.A, P.window);
     NLOS_REQUIRE(smem <= 227 * 1024, "%s: %zu B of shared memory needed (A=%d, window=%d) > 227 KB", name, smem, P.A, P.window);

@@ -35,17 +35,19 @@ struct TransientParams {
     const unsigned* list;            // entries g | e << NLOS_ENTRY_SHIFT, tile-major, ordered by bucket
     const unsigned* list_bins;       // per entry: tile-level shell klo | khi << 16 (binning.cu:shell_fill_kernel)
     const long long* cell_offsets;   // [n_tiles*cpt + 1], cpt = n_classes * n_buckets cells per tile (class-major); this launch walks cells [cell0, cell0 + n_buckets)
-    int cpt, cell0;
+    int cpt;
+    // a launch walks one or two SEGMENTS = entry classes rendered by the same kernel: cells [seg_cell0[s], seg_cell0[s] + n_buckets) of every tile
+    int n_seg, seg_cell0[2];
     long long list_capacity;         // entries the list buffers hold
-    int* work;                       // [n_tiles] next slice of every tile's entry list (zeroed before the launch)
+    int* work;                       // [n_seg*n_tiles] next slice of every (segment, tile) entry list (zeroed before the launch)
     float t0, dt, inv_dt;
     int T, window, bucket, n_buckets, slice_len;
     float flush_scale;   // c*deltaT for the numerical mode (volume_renderer.cu:182), 1 for the analytic-exact mode
     float mcut2;
-    int one_pass;        // analytic mode, time-wide entries: every ray is a 1-node ray, H / gH are the UNWEIGHTED bin rows (no 1/(r^2+1e-8)):
+    int seg_one_pass[2]; // analytic mode, time-wide entries: every ray is a 1-node ray, H / gH are the UNWEIGHTED bin rows (no 1/(r^2+1e-8)):
                          // the fixed 7-tap filter of analytic_filter_kernel and the radial weight are applied to the whole row outside
-    float* H;            // forward out   [n_tiles*32, T]  (accumulated with REDs; caller zeroes)
-    const float* gH;     // backward in   [n_tiles*32, T]
+    float* seg_H[2];        // forward out per segment  [n_tiles*32, T]  (accumulated with REDs; caller zeroes)
+    const float* seg_gH[2]; // backward in per segment  [n_tiles*32, T]
     float* dacc;         // backward out  [N, 16]          (accumulated with REDs; caller zeroes)
     const float* sh;     // raw SH coefficients [N, sh_dim] (used when sh_degree > 0: per (Gaussian, scan point) albedo, volume_renderer.cu:107-111)
     int sh_dim, sh_degree;

@@ -97,7 +97,7 @@ class TransientRenderer:
         self.cell_counts = torch.empty(n_cells, dtype=torch.int32, device=dev)
         self.cell_offsets = torch.empty(n_cells + 1, dtype=torch.int64, device=dev)
         self.tile_items = torch.empty(self.geom.n_tiles + 1, dtype=torch.int32, device=dev)
-        self.work = torch.empty(self.geom.n_tiles, dtype=torch.int32, device=dev)      # per-tile slice counters (work stealing)
+        self.work = torch.empty(2 * self.geom.n_tiles, dtype=torch.int32, device=dev)  # per-(segment, tile) slice counters (work stealing)
         self.header = torch.zeros(4, dtype=torch.int64, device=dev)
         self.header_host = torch.zeros(4, dtype=torch.int64).pin_memory()
         self.dacc = torch.empty(N, L.nlosb200_grad_floats(), dtype=torch.float32, device=dev)
@@ -184,14 +184,28 @@ class TransientRenderer:
         return self.last_total
 
     def _launches(self):
-        """(cls, variant, one_pass) of the render launches, one per entry class: class = footprint bit + n_fp * time-wide bit.  Footprint bit 0 =
-        narrow entries -> direct-to-window kernel, 1 = wide -> register accumulators; time-wide entries render one-pass."""
+        """(cls, variant, one_pass) per entry class: class = footprint bit + n_fp * time-wide bit.  Footprint bit 0 = narrow entries ->
+        direct-to-window kernel, 1 = wide -> register accumulators; time-wide entries render one-pass."""
         out = []
         for tw in range(self.n_tw):
             for fp in range(self.n_fp):
                 var = (1 if fp == 0 else 0) if self.n_fp == 2 else self.variant
                 out.append((fp + self.n_fp * tw, var, tw))
         return tuple(out)
+
+    def _launch_groups(self):
+        """Render launches: the classes of one kernel variant go into ONE launch as its (up to two) segments, so a pass is one launch per
+        kernel and the CTAs that drain one class move on to the other instead of idling to the launch boundary.  The deterministic mode
+        keeps one class per launch (its per-tile partial buffers are owned by one warp at a time)."""
+        groups = []
+        for cls, var, op in self._launches():
+            for g in groups:
+                if g[0] == var and len(g[1]) < 2 and not self.deterministic:
+                    g[1].append((cls, op))
+                    break
+            else:
+                groups.append((var, [(cls, op)]))
+        return groups
 
     def _render_args(self, cls):
         g = self.geom
@@ -205,13 +219,12 @@ class TransientRenderer:
 
     def forward_tiled(self):
         """-> H [n_tiles*32, T] in tile-major scan order (after prepare())."""
-        H = torch.empty(self.geom.n_tiles * TILE, self.T, dtype=torch.float32, device=self.records.device)
-        Ha = torch.empty_like(H) if self.one_pass else None          # unweighted one-node rows of the time-wide entries
-        seen = [False, False]
-        for cls, var, op in self._launches():
-            _lib.call("nlosb200_transient_forward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, op, int(seen[op]),
-                      *self._sh_args(), (Ha if op else H).data_ptr(), _lib.stream())
-            seen[op] = True
+        H = torch.zeros(self.geom.n_tiles * TILE, self.T, dtype=torch.float32, device=self.records.device)
+        Ha = torch.zeros_like(H) if self.one_pass else None          # unweighted one-node rows of the time-wide entries
+        for var, segs in self._launch_groups():
+            (cls, op), (cls2, op2) = segs[0], (segs[1] if len(segs) > 1 else (-1, 0))
+            _lib.call("nlosb200_transient_forward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, op, 1,
+                      *self._sh_args(), (Ha if op else H).data_ptr(), cls2, op2, (Ha if op2 else H).data_ptr(), _lib.stream())
         if self.one_pass:
             _lib.call("nlosb200_analytic_filter", Ha.data_ptr(), H.data_ptr(), H.shape[0], self.T, self.t0, self.dt, 0, _lib.stream())
         return H
@@ -230,10 +243,11 @@ class TransientRenderer:
         if self.one_pass:                                            # weights of the one-pass launches: F(w gH)
             gHa = torch.empty_like(gH_tiled)
             _lib.call("nlosb200_analytic_filter", gH_tiled.data_ptr(), gHa.data_ptr(), gH_tiled.shape[0], self.T, self.t0, self.dt, 1, _lib.stream())
-        for n, (cls, var, op) in enumerate(self._launches()):
+        for n, (var, segs) in enumerate(self._launch_groups()):
+            (cls, op), (cls2, op2) = segs[0], (segs[1] if len(segs) > 1 else (-1, 0))
             _lib.call("nlosb200_transient_backward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, op, int(n > 0),
-                      *self._sh_args(), (gHa if op else gH_tiled).data_ptr(), dacc.data_ptr(), dsh.data_ptr() if dsh is not None else None, int(det),
-                      _lib.stream())
+                      *self._sh_args(), (gHa if op else gH_tiled).data_ptr(), cls2, op2, (gHa if op2 else gH_tiled).data_ptr(),
+                      dacc.data_ptr(), dsh.data_ptr() if dsh is not None else None, int(det), _lib.stream())
         if det:
             _lib.call("nlosb200_reduce_tile_partials", dacc.data_ptr(), self.geom.n_tiles, self.dacc.numel(), self.dacc.data_ptr(), _lib.stream())
             if dsh is not None:

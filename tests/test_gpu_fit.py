@@ -14,7 +14,7 @@ pytestmark = pytest.mark.gpu
 def test_fitting_loop_reduces_the_loss(mode):
     N, Sy, Sx, T, A = 300, 8, 8, 64, 8
     geom, ta, truth = util.small_scene(N, Sy, Sx, T, A, scale_mul=2.0, device="cuda")
-    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode)
+    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, one_pass=True)
     target = r.forward(*truth).clone()
     g = torch.Generator(device="cuda").manual_seed(5)
     start = [p.clone() for p in truth]

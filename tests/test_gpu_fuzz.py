@@ -38,7 +38,7 @@ def test_random_scene_forward_and_lists(seed):
     geom, ta, params = util.small_scene(N, Sy, Sx, T, A, seed=100 + seed, scale_mul=scale_mul, device="cuda")
     r = None
     for mode, m in (("numerical", 0), ("analytic", 1)):
-        kw = dict(mode=mode, window=window, bucket=bucket, slice_len=slice_len)
+        kw = dict(mode=mode, window=window, bucket=bucket, slice_len=slice_len, one_pass=True)
         r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], **kw)
         H = r.forward(*params).cpu().numpy().reshape(Sy * Sx, T)
         H64 = util.oracle_H(geom, ta, params, mode=m, precision="f64")
@@ -74,7 +74,7 @@ def test_random_scene_backward(seed, mode):
     m = 0 if mode == "numerical" else 1
     gH = torch.rand(Sy, Sx, T, generator=torch.Generator().manual_seed(seed))
     ps = [p.clone().requires_grad_() for p in params]
-    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, window=window, bucket=bucket, slice_len=slice_len)
+    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, window=window, bucket=bucket, slice_len=slice_len, one_pass=True)
     H = render_transient_batch(r, *ps)
     (H * gH.cuda()).sum().backward()
     cg = scenes_cpu(geom)

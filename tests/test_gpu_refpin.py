@@ -68,10 +68,13 @@ def test_analytic_exact_is_the_bin_integral_of_the_reference_pdf(scale_mul):
     Hq = I / (rk[None, :] ** 2 + 1e-8)                                          # attenuation at the bin centre (cuda_autograd.py:308)
     assert Hq.max() > 0
     Ho = util.oracle_H(cg, ta, params, mode=1, precision="f64")                 # the oracle's closed form
-    Hg = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode="analytic").forward(*params).cpu().numpy().reshape(cg.S, T)
-    e_o, e_g = util.rel_to_max(Ho, Hq), util.rel_to_max(Hg, Hq)
-    print(f"scale x{scale_mul}: closed form vs quadrature of the reference pdf {e_o:.2e}; GPU vs quadrature {e_g:.2e}")
-    assert e_o < 2e-5 and e_g < TOL
+    e_o = util.rel_to_max(Ho, Hq)
+    assert e_o < 2e-5
+    for one_pass in (False, True):                                              # the mixture plan and the one-pass (1-node rows + 7-tap filter) plan
+        Hg = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode="analytic", one_pass=one_pass).forward(*params)
+        e_g = util.rel_to_max(Hg.cpu().numpy().reshape(cg.S, T), Hq)
+        print(f"scale x{scale_mul}: closed form vs quadrature of the reference pdf {e_o:.2e}; GPU (one_pass={one_pass}) vs quadrature {e_g:.2e}")
+        assert e_g < TOL
 
 
 @needs_ref
@@ -102,7 +105,7 @@ def test_gradients_match_finite_differences_of_the_reference_forward(mode):
 
     # GPU gradients
     ps = [p.clone().requires_grad_() for p in params]
-    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode)
+    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, one_pass=True)
     (render_transient_batch(r, *ps) * gH.float().cuda()).sum().backward()
     # the reference's per-ray lists at the base point == the membership the GPU used (cap not binding: 8 Gaussians)
     steps = FD_STEPS
@@ -153,7 +156,7 @@ def test_sampled_scan_points_of_the_timed_configurations_match_the_oracle(cfg, r
     sub = lambda x: f(x)[pts]
     oracle.set_num_threads(__import__("os").cpu_count() or 1)
     for mode, m in (("numerical", 0), ("analytic", 1)):
-        H = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode).forward(*[p.cuda() for p in params])
+        H = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, one_pass=True).forward(*[p.cuda() for p in params])
         H = H.reshape(full.S, T)[pts].cpu().numpy()
         torch.cuda.empty_cache()
         H64 = oracle.transient_batch(sub(full.scan_o), sub(full.sin_th), sub(full.cos_th), sub(full.sin_ph), sub(full.cos_ph), f(ta["t_samples"]),

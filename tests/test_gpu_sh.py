@@ -30,7 +30,7 @@ def _scene(N, Sy, Sx, T, A, deg, scale_mul=2.0, seed=3):
 def test_batched_forward_matches_oracle(deg, mode, variant):
     N, Sy, Sx, T, A = 200, 5, 9, 48, 6
     geom, ta, params = _scene(N, Sy, Sx, T, A, deg)
-    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, variant=variant, active_sh_degree=deg)
+    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, variant=variant, active_sh_degree=deg, one_pass=True)
     H = r.forward(*params).cpu().numpy().reshape(Sy * Sx, T)
     H64 = util.oracle_H(scenes_cpu(geom), ta, [p.cpu() for p in params], mode=0 if mode == "numerical" else 1, precision="f64", sh_degree=deg)
     H0 = util.oracle_H(scenes_cpu(geom), ta, [p.cpu() for p in params], mode=0 if mode == "numerical" else 1, precision="f64", sh_degree=0)
@@ -46,7 +46,7 @@ def test_batched_backward_matches_autograd(deg, mode, variant):
     geom, ta, params = _scene(N, Sy, Sx, T, A, deg)
     gH = torch.rand(Sy, Sx, T, generator=torch.Generator().manual_seed(5))
     ps = [p.clone().requires_grad_() for p in params]
-    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, variant=variant, active_sh_degree=deg)
+    r = TransientRenderer(geom, T, ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, variant=variant, active_sh_degree=deg, one_pass=True)
     H = render_transient_batch(r, *ps)
     (H * gH.cuda()).sum().backward()
     cg = scenes_cpu(geom)

@@ -21,7 +21,7 @@ VARIANTS = ("auto", "wide", "narrow")
 
 
 def _renderer(geom, ta, mode, **kw):
-    return TransientRenderer(geom, ta["t_samples"].numel(), ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, **kw)
+    return TransientRenderer(geom, ta["t_samples"].numel(), ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, **{"one_pass": True, **kw})
 
 
 @pytest.mark.parametrize("shape,scale_mul", [((150, 5, 9, 48, 6), 1.0), ((1000, 16, 16, 128, 8), 1.0), ((400, 8, 8, 200, 8), 1.0),

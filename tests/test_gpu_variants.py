@@ -12,7 +12,7 @@ pytestmark = pytest.mark.gpu
 
 
 def _r(geom, ta, mode, **kw):
-    return TransientRenderer(geom, ta["t_samples"].numel(), ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, **kw)
+    return TransientRenderer(geom, ta["t_samples"].numel(), ta["t0"], ta["dt"], ta["c"] * ta["deltaT"], mode=mode, **{"one_pass": True, **kw})
 
 
 @pytest.mark.parametrize("variant", ["wide", "narrow", "auto"])
@@ -62,6 +62,32 @@ def test_variants_agree(mode, scale_mul):
         for a, b in zip(outs[v][1], outs["wide"][1]):
             if np.abs(b).max() > 0:
                 assert util.rel_to_max(a, b) < 3e-5
+
+
+@pytest.mark.parametrize("scale_mul", [0.5, 1.0, 3.0])
+def test_analytic_plans_agree(scale_mul):
+    """analytic-exact mode: the mixture plan (one_pass=False: the default below 64 tiles) and the one-pass plan (time-wide entries as 1-node
+    rows + the fixed 7-tap filter, merged two-class launches) give the same histograms and gradients; the deterministic mode (one class per
+    launch) as well."""
+    N, Sy, Sx, T, A = 400, 6, 10, 160, 10
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=scale_mul, device="cuda")
+    gH = torch.rand(Sy, Sx, T, generator=torch.Generator().manual_seed(3)).cuda()
+    outs = []
+    for kw in (dict(one_pass=False), dict(one_pass=True), dict(one_pass=True, deterministic=True), dict(one_pass=None)):
+        r = _r(geom, ta, "analytic", **kw)
+        if kw["one_pass"]:
+            assert r.n_classes == 4 and len(r._launch_groups()) == (4 if r.deterministic else 2)
+        else:
+            assert not r.one_pass and r.n_classes == 2                   # 2 tiles < 64: the plan is off by default
+        ps = [p.clone().requires_grad_() for p in params]
+        H = render_transient_batch(r, *ps)
+        (H * gH).sum().backward()
+        outs.append((H.detach().cpu().numpy(), [p.grad.cpu().numpy() for p in ps]))
+    for H, g in outs[1:]:
+        assert util.rel_to_max(H, outs[0][0]) < 4e-5                     # 2 x the 1.6e-5-of-a-ray's-peak bound of the filter
+        for a, b in zip(g, outs[0][1]):
+            if np.abs(b).max() > 0:
+                assert util.rel_to_max(a, b) < 1e-4
 
 
 def test_backward_after_another_forward_uses_its_own_lists():
