@@ -95,13 +95,18 @@ int nlosb200_transient_forward(const float* tiles, int n_tiles, int A, const flo
                                const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
                                int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H,
-                               int cls2, int one_pass2, float* H2, void* stream);
+                               int cls2, int one_pass2, float* H2, unsigned short* hit_stash, void* stream);
 int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                 const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                 int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
                                 int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree,
                                 const float* grad_H, int cls2, int one_pass2, const float* grad_H2, float* dacc, float* dsh,
-                                int per_tile_partials, void* stream);
+                                int per_tile_partials, const unsigned short* hit_stash, void* stream);
+/* Culling words (variant 1 only, A <= 64; NULL = off): hit_stash [list_capacity][32] uint16, 16-byte aligned.  A forward launch writes, for every
+ * (list entry, scan point) it renders, the anchor of the candidate block and the bit-exact hit mask of its <= 2 x 2 rays (i0 | j0 << 6 | mask << 12;
+ * 0xFFFF marks an entry with a wider rectangle); a backward launch over the SAME lists and records reads them instead of repeating the footprint
+ * rectangle and the slab tests (-15 % of its instructions on cfg4).  The caller passes the pointer to the backward only after a forward of the same
+ * prepare() has filled it. */
 /* One-pass analytic plan (mode 1, launches over the TIME-WIDE entry classes of the binning: smallest scale >= 1.3 bins): one_pass = 1 renders
  * every ray with the 1-node mixture and leaves the 1/(r^2+1e-8) weight out -- H is then a buffer Ha of unweighted rows, and
  *   forward : nlosb200_analytic_filter(Ha, H, rows, T, t0, dt, 0)   adds  w F(Ha)  to H   (F = the fixed 7-tap filter that turns 1-node rows into
@@ -194,6 +199,14 @@ int nlosb200_mse_loss_grad(const float* H, const float* target, long long n, flo
  * step = 1, 2, ... selects the bias corrections.  Same operation order as torch.optim.Adam's single-tensor path. */
 int nlosb200_adam_step(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg, float* const* exp_avg_sq,
                        const long long* sizes, const float* lrs, float beta1, float beta2, float eps, int step, void* stream);
+
+/* ==== MCMC relocation helper (GaussianModel._update_params, gaussian_model/gaussian_model.py:471-483, calls compute_relocation_cuda -- a name
+ * the reference never defines: the helper of the public 3DGS-MCMC code, not vendored; PARITY UNPINNED, restated from the publication, eq. 9):
+ *   opacity_new = 1 - (1 - opacity_old)^(1/N) ;  scale_new = scale_old * opacity_old / sum_{i=1..N} sum_{k<i} C(i-1,k) (-1)^k opacity_new^(k+1) / sqrt(k+1)
+ * counts N [P] int32 (clamped to [1, n_max-1]), binoms [n_max, n_max] float with C(n,k) at [n*n_max+k], n_max <= 64; activated values in
+ * and out: opacity [P], scale [P,3]. */
+int nlosb200_compute_relocation(const float* opacity_old, const float* scale_old, const int* counts, const float* binoms, int n_max, int P,
+                                float* opacity_new, float* scale_new, void* stream);
 
 /* ==== dense evaluation of the mixture at arbitrary points: density = sum_g pdf_g sigmoid(o_g), rho_density = sum_g pdf_g sigmoid(o_g) albedo_g over
  * ALL Gaussians (GaussianModel.estimate_rho_w_no_occlusion(out_separately=True), gaussian_model/gaussian_model.py:346-364, as used by the volume

@@ -68,3 +68,50 @@ extern "C" int nlosb200_adam_step(int n_tensors, float* const* params, const flo
     NLOS_CHECK_LAUNCH("adam_multi_kernel");
     return 0;
 }
+
+// ==== MCMC relocation: opacity / scale of a Gaussian that is replaced by N copies of itself ============================================
+// GaussianModel._update_params (/root/reference/gaussian_model/gaussian_model.py:471-483) calls compute_relocation_cuda(opacity_old,
+// scale_old, N), a name the reference never defines or imports ("broken"): it is the helper of the public
+// 3DGS-MCMC code (Kheradmand et al., "3D Gaussian Splatting as Markov Chain Monte Carlo", NeurIPS 2024, eq. 9), which is not vendored
+// under /root/reference.  PARITY UNPINNED: restated from the publication --
+//     o_new = 1 - (1 - o_old)^(1/N)
+//     s_new = s_old * o_old / sum_{i=1..N} sum_{k=0..i-1} C(i-1, k) (-1)^k o_new^(k+1) / sqrt(k+1)
+// with the counts clamped to [1, n_max - 1] (n_max = 51 upstream) and the binomial table C(n, k) = binoms[n * n_max + k] passed in.
+// The summation keeps the published order (i outer, k inner, float accumulator) because the series alternates with binomial-sized
+// terms: its float rounding IS the function for large N.  The k-dependent factor is formed once per k (double, as an int-argument
+// pow / sqrt evaluates upstream) instead of once per (i, k): O(N) transcendental work, O(N^2 / 2) fused multiply-adds.
+#define RELOC_MAX_N 64
+__global__ void __launch_bounds__(128) relocation_kernel(const float* __restrict__ opacity_old, const float* __restrict__ scale_old,
+                                                         const int* __restrict__ counts, const float* __restrict__ binoms, int n_max, int P,
+                                                         float* __restrict__ opacity_new, float* __restrict__ scale_new)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const int N = min(max(counts[idx], 1), n_max - 1);
+    const float o_old = opacity_old[idx];
+    const float o_new = 1.0f - powf(1.0f - o_old, 1.0f / (float)N);
+    opacity_new[idx] = o_new;
+    double term[RELOC_MAX_N];
+    double pw = (double)o_new;                               // o_new^(k+1)
+    for (int k = 0; k < N; ++k) {
+        term[k] = ((k & 1) ? -1.0 : 1.0) / sqrt((double)(k + 1)) * pw;
+        pw *= (double)o_new;
+    }
+    float denom = 0.f;
+    for (int i = 1; i <= N; ++i)
+        for (int k = 0; k < i; ++k) denom = (float)((double)denom + (double)binoms[(size_t)(i - 1) * n_max + k] * term[k]);
+    const float coeff = o_old / denom;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) scale_new[(size_t)idx * 3 + a] = coeff * scale_old[(size_t)idx * 3 + a];
+}
+
+extern "C" int nlosb200_compute_relocation(const float* opacity_old, const float* scale_old, const int* counts, const float* binoms, int n_max,
+                                           int P, float* opacity_new, float* scale_new, void* stream)
+{
+    NLOS_REQUIRE(P >= 0 && n_max >= 2 && n_max <= RELOC_MAX_N, "compute_relocation: n_max=%d not in [2, %d]", n_max, RELOC_MAX_N);
+    if (P == 0) return 0;
+    NLOS_REQUIRE(opacity_old && scale_old && counts && binoms && opacity_new && scale_new, "compute_relocation: null pointer");
+    relocation_kernel<<<(P + 127) / 128, 128, 0, (cudaStream_t)stream>>>(opacity_old, scale_old, counts, binoms, n_max, P, opacity_new, scale_new);
+    NLOS_CHECK_LAUNCH("relocation_kernel");
+    return 0;
+}

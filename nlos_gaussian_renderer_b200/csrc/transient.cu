@@ -904,7 +904,7 @@ static int fill_params(TransientParams& P, const float* tiles, int n_tiles, int 
     P.n_seg = cls2 >= 0 ? 2 : 1; P.seg_cell0[0] = cls * P.n_buckets; P.seg_cell0[1] = (cls2 >= 0 ? cls2 : cls) * P.n_buckets;
     P.seg_one_pass[0] = one_pass; P.seg_one_pass[1] = one_pass2;
     P.slice_len = slice_len; P.flush_scale = mode == MODE_NUM ? c_deltaT : 1.0f; P.mcut2 = mcut * mcut;
-    P.seg_H[0] = P.seg_H[1] = nullptr; P.seg_gH[0] = P.seg_gH[1] = nullptr; P.dacc = nullptr; P.counters = nullptr; P.hit_dump = g_hit_dump;
+    P.seg_H[0] = P.seg_H[1] = nullptr; P.seg_gH[0] = P.seg_gH[1] = nullptr; P.dacc = nullptr; P.counters = nullptr; P.hit_dump = g_hit_dump; P.hit_stash = nullptr;
     P.sh = sh; P.sh_dim = sh_dim; P.sh_degree = sh_degree; P.dsh = nullptr; P.part_stride = 0;
     return 0;
 }
@@ -915,7 +915,7 @@ extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A
                                           const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                           int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
                                           int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H,
-                                          int cls2, int one_pass2, float* H2, void* stream)
+                                          int cls2, int one_pass2, float* H2, unsigned short* hit_stash, void* stream)
 {
     TransientParams P;
     int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
@@ -929,6 +929,8 @@ extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A
         NLOS_REQUIRE(e == cudaSuccess, "transient_forward: memset: %s", cudaGetErrorString(e));
     }
     P.seg_H[0] = H; P.seg_H[1] = cls2 >= 0 ? H2 : H;
+    NLOS_REQUIRE(!hit_stash || (A <= 64 && ((uintptr_t)hit_stash % 16) == 0), "transient_forward: culling words need A <= 64 (A=%d) and 16-byte alignment", A);
+    P.hit_stash = variant == 1 ? hit_stash : nullptr;
     if (variant == 1) return launch_transient_narrow(P, mode, false, s);
     return mode == MODE_NUM ? launch_transient<MODE_NUM, false>(P, s, "transient_kernel<num,fwd>")
                             : launch_transient<MODE_ANA, false>(P, s, "transient_kernel<ana,fwd>");
@@ -939,7 +941,7 @@ extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int 
                                            int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
                                            int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree,
                                            const float* grad_H, int cls2, int one_pass2, const float* grad_H2, float* dacc, float* dsh,
-                                           int per_tile_partials, void* stream)
+                                           int per_tile_partials, const unsigned short* hit_stash, void* stream)
 {
     TransientParams P;
     int rc = fill_params(P, tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T, window,
@@ -961,6 +963,8 @@ extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int 
     P.dacc = dacc;
     P.dsh = dsh;
     P.part_stride = per_tile_partials ? (size_t)N * NLOS_GRAD_FLOATS : 0;
+    NLOS_REQUIRE(!hit_stash || (A <= 64 && ((uintptr_t)hit_stash % 16) == 0), "transient_backward: culling words need A <= 64 (A=%d) and 16-byte alignment", A);
+    P.hit_stash = variant == 1 ? const_cast<unsigned short*>(hit_stash) : nullptr;
     if (variant == 1) return launch_transient_narrow(P, mode, true, s);
     return mode == MODE_NUM ? launch_transient<MODE_NUM, true>(P, s, "transient_kernel<num,bwd>")
                             : launch_transient<MODE_ANA, true>(P, s, "transient_kernel<ana,bwd>");

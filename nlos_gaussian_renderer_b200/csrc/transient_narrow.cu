@@ -29,6 +29,8 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
     float* s_ring = s_H + TR_WPB * wstride;                             // [TR_WPB][TR_STAGES][TR_RING][32]
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_ring + TR_WPB * TR_STAGES * TR_RING * NLOS_REC_FLOATS);   // [1 + TR_WPB*TR_STAGES]
     int* s_ctl = reinterpret_cast<int*>(s_bar + 1 + TR_WPB * TR_STAGES);                                      // [2] next tile, tiles consumed
+    // staging of the culling words of a ring batch (backward): [TR_WPB][TR_STAGES][TR_RING][32] u16, 16-byte aligned
+    unsigned short* s_stash = reinterpret_cast<unsigned short*>((reinterpret_cast<uintptr_t>(s_ctl + 2) + 15) & ~(uintptr_t)15);
 
     if (P.cell_offsets[(size_t)P.n_tiles * P.cpt] > P.list_capacity) return;   // list buffer overflow (flagged by bin_window_fill): render nothing
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -40,6 +42,11 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
     float* Hw = s_H + warp * wstride + TR_GUARD * NLOS_TILE;            // bin `base` of this warp's window
     float* ring = s_ring + warp * TR_STAGES * TR_RING * NLOS_REC_FLOATS;
     uint64_t* bar = s_bar + 1 + warp * TR_STAGES;
+    // ---- culling words: the forward pass leaves, per (entry, scan point), the anchor of the candidate block and the bit-exact hit mask of
+    //      its <= 2 x 2 rays in P.hit_stash (i0 | j0 << 6 | mask << 12; 0xFFFF = "entry with a wider rectangle: decide again"); the backward
+    //      pass of the same lists reads them instead of repeating the footprint rectangle and the slab tests
+    unsigned short* const stash_w = s_stash + warp * TR_STAGES * TR_RING * NLOS_TILE;
+    const bool st_rd = BWD && P.hit_stash != nullptr, st_wr = FWD && P.hit_stash != nullptr;
     for (int i = lane; i < wstride; i += 32) Hw[i - TR_GUARD * NLOS_TILE] = 0.f;
     __syncthreads();
 
@@ -171,8 +178,11 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                 // (no proxy fence: the stage is only ever READ through the generic proxy, and those reads were consumed before the
                 //  __syncwarp below; fence.proxy.async is MEMBAR.ALL.CTA + FENCE.VIEW.ASYNC, i.e. it would wait for this warp's
                 //  outstanding gradient / histogram REDs every 4 entries -- 15 % of the backward's stall samples)
-                if (lane == 0) mbar_arrive_expect_tx(&bar[stage], (uint32_t)cnt * NLOS_REC_FLOATS * 4u);
+                if (lane == 0) mbar_arrive_expect_tx(&bar[stage], (uint32_t)cnt * (NLOS_REC_FLOATS * 4u + (st_rd ? NLOS_TILE * 2u : 0u)));
                 __syncwarp();
+                if (st_rd && lane == 0)      // the batch's entries are consecutive list positions: one copy of cnt x 64 B
+                    bulk_g2s(stash_w + stage * TR_RING * NLOS_TILE, P.hit_stash + (size_t)(beg + b * TR_RING) * NLOS_TILE, (uint32_t)cnt * NLOS_TILE * 2u,
+                             &bar[stage]);
                 ent_next = 0;
                 if (lane < cnt) {
                     ent_next = P.list[beg + b * TR_RING + lane];
@@ -241,7 +251,14 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     //      (eigenvalues +-1/r^2 and cot(theta)/r^2 for theta, +-1/rho^2 for phi) and rho >= rho_min = rho - Rb over the box.
                     //      Twice that bound is used; boxes with Rb > rho / 2 (never for a relay wall in the plane y = 0) take every ray.
                     int i0 = 0, i1 = -1, j0 = 0, j1 = -1;
-                    if (act) {
+                    unsigned pm = 0;            // culling word: the hit mask of the 2 x 2 block anchored at (i0, j0)
+                    bool use_st = false;
+                    if (st_rd) {
+                        const unsigned stw = stash_w[((rb & 1u) * TR_RING + q) * NLOS_TILE + lane];
+                        use_st = __all_sync(0xffffffffu, stw != 0xFFFFu);                       // (the marker is written by whole warps)
+                        if (use_st) { i0 = (int)(stw & 63u); j0 = (int)((stw >> 6) & 63u); i1 = i0 + 1; j1 = j0 + 1; pm = stw >> 12; }
+                    }
+                    if (!use_st && act) {
                         i1 = A - 1; j1 = A - 1;
                         const float rho2 = fmaf(cx, cx, cy * cy), Rb = v6.w;
                         const float irho = rsqrt_approx(fmaxf(rho2, 1e-30f)), rho = rho2 * irho, rmin = rho - Rb;
@@ -461,8 +478,11 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                             };
                             // phase 1: both directions inside the entry (zmin is a multiple of 4) -- the bare loop
                             const int n1 = min(nst, zmin);
+                            // (two blocks per iteration: the register allocator tends to rotate the six prefix-sum accumulators with a dozen
+                            //  MOVs at the back edge of this loop; over 8 steps they cost a quarter of what they cost over 4)
 #pragma unroll 1
-                            for (; s < n1; s += 4) block4();
+                            for (; s + 8 <= n1; s += 8) { block4(); block4(); }
+                            if (s < n1) { block4(); s += 4; }
                             // phase 2 (rare): one direction has left the entry and is switched off
 #pragma unroll 1
                             for (; s < nst; s += 4) {
@@ -487,16 +507,19 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     //      which grows with 1/|d_axis|), so the two forms can only disagree where |tmax - tmin| <= 2 k |tmax| / (1 - k): those
                     //      candidates (band 2.5 k |tmax|; every candidate of a block with k > 0.05) are decided again by the reference's own
                     //      expression (ray_aabb_x): bit-exact hit masks.
-                    const bool fast2 = __all_sync(0xffffffffu, !act || (i1 - i0 <= 1 && j1 - j0 <= 1));
+                    const bool fast2 = use_st || __all_sync(0xffffffffu, !act || (i1 - i0 <= 1 && j1 - j0 <= 1));
                     const float kband = 1.5e-8f * s_pi[PI_ISTMAX * 32 + lane];      // band of the slab test per unit of 1/|d_axis|
                     int ib = i0, jb = j0;
-                    bool more = act && i0 <= i1 && j0 <= j1;
+                    bool more = use_st ? (act && pm != 0u) : (act && i0 <= i1 && j0 <= j1);
+                    unsigned stash_out = fast2 ? 0u : 0xFFFFu;
                     while (__any_sync(0xffffffffu, more)) {
                         const float* const thb = tabl + TAB_TH(A, more ? ib : 0);
                         const float* const phb = tabl + TAB_PH(A, more ? jb : 0);
                         unsigned mask = 0, border = 0;
                         if (more) {
-                            if (fast2) {
+                            if (use_st) {
+                                mask = (pm & 3u) | ((pm & 12u) << 6);                      // rays (0,0) (0,1) (1,0) (1,1) -> bits 0, 1, 8, 9
+                            } else if (fast2) {
                                 const bool r1 = i1 > ib, c1 = j1 > jb;
                                 const float icp0 = phb[PH_ICOS], isp0 = phb[PH_ISIN], icp1 = phb[128 + PH_ICOS], isp1 = phb[128 + PH_ISIN];
                                 const float tth0 = thb[TH_TAN], tth1 = thb[96 + TH_TAN];
@@ -583,6 +606,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                                 const bool h = ray_aabb_x(ox, oy, oz, __fmul_rn(thp[TH_SIN], php[PH_COS]), __fmul_rn(thp[TH_SIN], php[PH_SIN]), thp[TH_COS], box);
                                 mask = h ? (mask | (1u << bb)) : (mask & ~(1u << bb));
                             }
+                            if (st_wr && fast2) stash_out = (unsigned)ib | ((unsigned)jb << 6) | (((mask & 3u) | ((mask >> 6) & 12u)) << 12);
                             if (P.hit_dump) {      // (tests only) dense membership [scan point][ray][Gaussian], compared bit for bit with the reference's filter lists
                                 for (unsigned m = mask; m; m &= m - 1) {
                                     const int bb = __ffs(m) - 1;
@@ -773,6 +797,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                             }
                         }
                     }
+                    if (st_wr) P.hit_stash[(size_t)(beg + b * TR_RING + q) * NLOS_TILE + lane] = (unsigned short)stash_out;
                     if (GRAD) {
                         {
                             gax += lo_of(pga[0]) + hi_of(pga[0]); gay += lo_of(pga[1]) + hi_of(pga[1]); gaz += lo_of(pga[2]) + hi_of(pga[2]);

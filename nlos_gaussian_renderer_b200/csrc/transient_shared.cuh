@@ -53,6 +53,8 @@ struct TransientParams {
     int sh_dim, sh_degree;
     size_t part_stride;  // 0, or N*16: deterministic mode -- dacc / dsh are per-TILE partial buffers [n_tiles][N][16], summed in tile order afterwards
     float* dsh;          // backward out [N, 16]: dL/d(SH coefficients) when sh_degree > 0 (REDs; caller zeroes)
+    unsigned short* hit_stash;      // narrow kernel: per (list position, scan point) culling words, written by the forward and read by the backward of
+                                    // the same lists (null: every pass decides for itself); needs A <= 64
     unsigned char* hit_dump;        // tests only (nlosb200_debug_hit_dump): dense slab-test membership [n_tiles*32][A*A][N], or null
     unsigned long long* counters;   // MODE_COUNT: [0] hit (g,ray) pairs, [1] W_s, [2] evaluated sample-evals, [3] W_b
 };
@@ -125,7 +127,7 @@ static inline size_t transient_smem_bytes(int A, int window)
 {
     size_t f = (size_t)(NLOS_NTAB * A + NLOS_PINFO_ROWS) * NLOS_TILE + (size_t)TR_WPB * (window + 2 * TR_GUARD) * NLOS_TILE +
                (size_t)TR_WPB * TR_STAGES * TR_RING * NLOS_REC_FLOATS;
-    return f * 4 + (1 + TR_WPB * TR_STAGES) * 8 + 32;
+    return f * 4 + (1 + TR_WPB * TR_STAGES) * 8 + 32 + 16 + (size_t)TR_WPB * TR_STAGES * TR_RING * NLOS_TILE * 2;   // (+ the culling-word staging)
 }
 static inline int transient_num_sms()
 {

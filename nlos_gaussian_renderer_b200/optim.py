@@ -46,3 +46,14 @@ class FusedAdam:
         lr = (C.c_float * n)(*lrs)
         _lib.call("nlosb200_adam_step", n, arr(ps), arr(gs), arr(ms), arr(vs), sizes, lr, float(self.betas[0]), float(self.betas[1]), self.eps,
                   self.t, _lib.stream())
+
+    @torch.no_grad()
+    def reset_state(self, inds=None):
+        """Zero both moments of every group at the rows `inds` (all rows when None) -- what GaussianModel.replace_tensors_to_optimizer does
+        to the sources of relocated / cloned Gaussians (gaussian_model/gaussian_model.py:432-458)."""
+        for st in self.state:
+            if inds is None:
+                st["exp_avg"].zero_(); st["exp_avg_sq"].zero_()
+            else:
+                st["exp_avg"][inds] = 0
+                st["exp_avg_sq"][inds] = 0

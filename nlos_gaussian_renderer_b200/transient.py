@@ -34,7 +34,7 @@ class TransientRenderer:
 
     def __init__(self, geom: ScanGeometry, T, t0, dt, c_deltaT, mode="numerical", window=96, bucket=None, slice_len=None,
                  mcut=5.3, scaling_modifier=1.0, sigma_bbox=3.0, variant="auto", narrow_rays=2.5, active_sh_degree=0,
-                 deterministic=False, one_pass=None, one_pass_min_bins=1.3):
+                 deterministic=False, one_pass=None, one_pass_min_bins=1.3, culling_words=None):
         """window: bins of the per-warp sliding accumulator (multiple of 8; 96 bins x 12 warps + tables fill the 227 KB of one SM); bucket: bins the window advances by
         (default max(8, next pow2 of T/64): at most 64 buckets); slice_len: list entries a warp pulls at a time from its
         tile's counter (default: 16..256, sized so that every warp of the persistent grid gets >= 32 slices).
@@ -76,6 +76,12 @@ class TransientRenderer:
         self.tw_min = float(one_pass_min_bins) * self.dt if self.one_pass else 0.0
         self.n_fp = 2 if self.variant == 2 else 1
         self.n_tw = 2 if self.one_pass else 1
+        # culling words: the forward of the narrow kernel leaves, per (list entry, scan point), the bit-exact hit mask of its <= 2 x 2 candidate
+        # rays; the backward of the same prepare() reads them instead of repeating the footprint rectangle and the slab tests (64 B per entry:
+        # 21 GB at cfg4).  None = on when the lattice allows (A <= 64) and the buffer stays under a quarter of the device memory.
+        self.culling_words = culling_words
+        self._stash = None
+        self._stash_gen = -1
         self.n_classes = self.n_fp * self.n_tw
         self._N = None
         self._list = None
@@ -141,6 +147,13 @@ class TransientRenderer:
         dev = self.records.device
         self._list = torch.empty(max(int(total * 1.25) + 1024, 1024), dtype=torch.int32, device=dev)
         self._list_bins = torch.empty_like(self._list)                # per entry: shell klo | khi << 16
+        self._stash, self._stash_gen = None, -1
+        want = self.culling_words
+        nbytes = self._list.numel() * TILE * 2
+        if want is None:
+            want = nbytes <= torch.cuda.get_device_properties(dev).total_memory // 4
+        if want and self.geom.A <= 64 and any(v == 1 for v, _ in self._launch_groups()):
+            self._stash = torch.empty(self._list.numel() * TILE, dtype=torch.int16, device=dev)
 
     def prepare(self, means, log_scales, rotations, opacities, features):
         """preprocess + shell binning for the current parameters.  Stream ordered: the first call sizes the list buffer with one 32-byte
@@ -224,7 +237,9 @@ class TransientRenderer:
         for var, segs in self._launch_groups():
             (cls, op), (cls2, op2) = segs[0], (segs[1] if len(segs) > 1 else (-1, 0))
             _lib.call("nlosb200_transient_forward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, op, 1,
-                      *self._sh_args(), (Ha if op else H).data_ptr(), cls2, op2, (Ha if op2 else H).data_ptr(), _lib.stream())
+                      *self._sh_args(), (Ha if op else H).data_ptr(), cls2, op2, (Ha if op2 else H).data_ptr(),
+                      self._stash.data_ptr() if self._stash is not None else None, _lib.stream())
+        self._stash_gen = self.generation if self._stash is not None else -1
         if self.one_pass:
             _lib.call("nlosb200_analytic_filter", Ha.data_ptr(), H.data_ptr(), H.shape[0], self.T, self.t0, self.dt, 0, _lib.stream())
         return H
@@ -247,7 +262,8 @@ class TransientRenderer:
             (cls, op), (cls2, op2) = segs[0], (segs[1] if len(segs) > 1 else (-1, 0))
             _lib.call("nlosb200_transient_backward", *self._render_args(cls), self.c_deltaT, self.mcut, self.mode, var, op, int(n > 0),
                       *self._sh_args(), (gHa if op else gH_tiled).data_ptr(), cls2, op2, (gHa if op2 else gH_tiled).data_ptr(),
-                      dacc.data_ptr(), dsh.data_ptr() if dsh is not None else None, int(det), _lib.stream())
+                      dacc.data_ptr(), dsh.data_ptr() if dsh is not None else None, int(det),
+                      self._stash.data_ptr() if (self._stash is not None and self._stash_gen == self.generation) else None, _lib.stream())
         if det:
             _lib.call("nlosb200_reduce_tile_partials", dacc.data_ptr(), self.geom.n_tiles, self.dacc.numel(), self.dacc.data_ptr(), _lib.stream())
             if dsh is not None:

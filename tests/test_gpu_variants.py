@@ -90,6 +90,44 @@ def test_analytic_plans_agree(scale_mul):
                 assert util.rel_to_max(a, b) < 1e-4
 
 
+@pytest.mark.parametrize("scale_mul", [0.3, 1.0])
+@pytest.mark.parametrize("mode", ["numerical", "analytic"])
+def test_culling_words(mode, scale_mul):
+    """The backward pass that reads the forward's culling words (narrow kernel: anchor + hit mask of the <= 2 x 2 candidate rays per (entry, scan
+    point)) uses exactly the hit masks the forward decided -- and, in the deterministic mode, produces bit-identical gradients to the backward
+    that decides again; a backward without a forward of the same prepare() must not read them."""
+    N, Sy, Sx, T, A = 300, 6, 10, 96, 12
+    geom, ta, params = util.small_scene(N, Sy, Sx, T, A, scale_mul=scale_mul, device="cuda")
+    r_on = _r(geom, ta, mode, culling_words=True, narrow_rays=2.5)
+    fwd_masks = util.hit_masks_gpu(r_on, params)
+    assert r_on._stash is not None and r_on._stash_gen == r_on.generation
+    words = r_on._stash[: r_on.check_lists() * 32].cpu().numpy().view(np.uint16)
+    assert (words != 0xFFFF).any() and ((words >> 12) != 0).any()                  # the words carry hits
+    bwd_masks = util.hit_masks_gpu(r_on, params, backward=True)
+    assert fwd_masks.sum() > 0 and np.array_equal(fwd_masks, bwd_masks)
+    gH = torch.rand(Sy, Sx, T, generator=torch.Generator().manual_seed(5)).cuda()
+    grads = {}
+    for cw in (True, False):
+        r = _r(geom, ta, mode, culling_words=cw, deterministic=True)
+        assert (r._stash is None) or cw
+        ps = [p.clone().requires_grad_() for p in params]
+        (render_transient_batch(r, *ps) * gH).sum().backward()
+        assert (r._stash is not None) == cw
+        grads[cw] = [p.grad.clone() for p in ps]
+    for a, b in zip(grads[True], grads[False]):
+        assert torch.equal(a, b)
+    # prepare() without a forward: the words of the previous scene are stale and must be ignored
+    r = _r(geom, ta, mode, culling_words=True, deterministic=True)
+    r.forward(*[p[:100].contiguous() for p in params])
+    r.prepare(*params)
+    assert r._stash_gen != r.generation
+    r.render_backward(geom.tile_grad(gH))
+    want = _r(geom, ta, mode, culling_words=False, deterministic=True)
+    want.prepare(*params)
+    want.render_backward(geom.tile_grad(gH))
+    assert torch.equal(r.dacc, want.dacc)
+
+
 def test_backward_after_another_forward_uses_its_own_lists():
     """a second forward() on the same renderer before the first graph's backward() must not corrupt the first gradients."""
     geom, ta, params = util.small_scene(200, 5, 9, 48, 6, device="cuda")

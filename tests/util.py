@@ -67,16 +67,22 @@ def oracle_window_lists(geom, ta, params, r):
     return oracle.window_lists(klo, khi, T, r.window, r.bucket, cls, n_classes=r.n_classes), cls
 
 
-def hit_masks_gpu(r, params):
-    """[S, A*A, N] bool: the slab-test membership the render kernels of renderer r actually used (debug dump of the forward launch)."""
+def hit_masks_gpu(r, params, backward=False):
+    """[S, A*A, N] bool: the slab-test membership the render kernels of renderer r actually used (debug dump of the forward launch; of the
+    backward launch after an undumped forward with backward=True -- the masks that pass then reads from the forward's culling words)."""
     from nlos_gaussian_renderer_b200 import _lib
     g = r.geom
     N = params[0].shape[0]
     dump = torch.zeros(g.n_tiles * 32, g.A * g.A, N, dtype=torch.uint8, device="cuda")
     r.prepare(*params)
+    if backward:
+        H = r.forward_tiled()
     _lib.call("nlosb200_debug_hit_dump", dump.data_ptr())
     try:
-        r.forward_tiled()
+        if backward:
+            r.render_backward(torch.ones_like(H))
+        else:
+            r.forward_tiled()
         torch.cuda.synchronize()
     finally:
         _lib.call("nlosb200_debug_hit_dump", None)
