@@ -478,11 +478,8 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                             };
                             // phase 1: both directions inside the entry (zmin is a multiple of 4) -- the bare loop
                             const int n1 = min(nst, zmin);
-                            // (two blocks per iteration: the register allocator tends to rotate the six prefix-sum accumulators with a dozen
-                            //  MOVs at the back edge of this loop; over 8 steps they cost a quarter of what they cost over 4)
 #pragma unroll 1
-                            for (; s + 8 <= n1; s += 8) { block4(); block4(); }
-                            if (s < n1) { block4(); s += 4; }
+                            for (; s < n1; s += 4) block4();
                             // phase 2 (rare): one direction has left the entry and is switched off
 #pragma unroll 1
                             for (; s < nst; s += 4) {
@@ -517,7 +514,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                         const float* const phb = tabl + TAB_PH(A, more ? jb : 0);
                         unsigned mask = 0, border = 0;
                         if (more) {
-                            if (use_st) {
+                            if (pm) {                                   // (pm != 0 only with use_st; testing pm keeps ptxas from rotating the backward loop's accumulators)
                                 mask = (pm & 3u) | ((pm & 12u) << 6);                      // rays (0,0) (0,1) (1,0) (1,1) -> bits 0, 1, 8, 9
                             } else if (fast2) {
                                 const bool r1 = i1 > ib, c1 = j1 > jb;
