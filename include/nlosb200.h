@@ -102,6 +102,19 @@ int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const fl
                                 int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree,
                                 const float* grad_H, int cls2, int one_pass2, const float* grad_H2, float* dacc, float* dsh,
                                 int per_tile_partials, const unsigned short* hit_stash, void* stream);
+/* nlosb200_transient_forward for callers that may not allocate (code under CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  It has NO counterpart in the reference.  Same arguments and results as
+ * nlosb200_transient_forward without `work` and `hit_stash`: the slice counters live in a static device array inside the library
+ * (nlosb200_transient_static_work_ints() = 65536 int32 = 256 KB per GPU that loads the library, held until exit), so the call performs no
+ * cudaMalloc / cudaFree and calls no allocating routine.  Limit: n_tiles * (2 if cls2 >= 0 else 1) <= 65536, otherwise an error is returned
+ * and nothing is launched.  Every call on a device shares the array (the counters a launch uses are zeroed first, stream ordered): calls
+ * that overlap on the GPU (different streams or host threads) race -- serialise them, or use nlosb200_transient_forward with own buffers. */
+int nlosb200_transient_static_work_ints(void);
+int nlosb200_transient_forward_static(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                                      const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
+                                      float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
+                                      int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim, int sh_degree, float* H,
+                                      int cls2, int one_pass2, float* H2, void* stream);
 /* Culling words (variant 1 only, A <= 64; NULL = off): hit_stash [list_capacity][32] uint16, 16-byte aligned.  A forward launch writes, for every
  * (list entry, scan point) it renders, the anchor of the candidate block and the bit-exact hit mask of its <= 2 x 2 rays (i0 | j0 << 6 | mask << 12;
  * 0xFFFF marks an entry with a wider rectangle); a backward launch over the SAME lists and records reads them instead of repeating the footprint

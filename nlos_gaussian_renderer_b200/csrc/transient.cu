@@ -936,6 +936,56 @@ extern "C" int nlosb200_transient_forward(const float* tiles, int n_tiles, int A
                             : launch_transient<MODE_ANA, false>(P, s, "transient_kernel<ana,fwd>");
 }
 
+// ---- the same forward for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart
+//      in the reference.  The one piece of scratch the forward needs -- the per-(segment, tile)
+//      slice counters `work` the persistent CTAs steal list slices from -- lives in a file-scope device array of a fixed maximum size
+//      (NLOS_STATIC_WORK_INTS int32 = 256 KB, held by every GPU that loads the library until exit) instead of a caller buffer.  In HOST
+//      code the name `g_static_work` is only a stand-in for the symbol: its device address is fetched once per device, with that device
+//      current, by cudaGetSymbolAddress and handed to the kernels as an ordinary pointer.  Every call shares the array (the launch zeroes
+//      the counters it uses first, stream ordered): calls that overlap on the GPU -- two streams, two host threads -- race on it.
+#define NLOS_STATIC_WORK_INTS 65536
+#define NLOS_STATIC_MAX_DEVICES 64
+static __device__ __align__(256) int g_static_work[NLOS_STATIC_WORK_INTS];
+static int* g_static_work_ptr[NLOS_STATIC_MAX_DEVICES];      // device address of g_static_work on each device (null: not fetched yet)
+
+static int static_work_address(int** out)
+{
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    NLOS_REQUIRE(e == cudaSuccess, "transient_forward_static: cudaGetDevice: %s", cudaGetErrorString(e));
+    NLOS_REQUIRE(dev >= 0 && dev < NLOS_STATIC_MAX_DEVICES, "transient_forward_static: device %d beyond the %d this entry point tracks", dev,
+                 NLOS_STATIC_MAX_DEVICES);
+    if (!g_static_work_ptr[dev]) {
+        int* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_static_work);       // (with `dev` current: the address is per device)
+        NLOS_REQUIRE(e == cudaSuccess && ptr, "transient_forward_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        g_static_work_ptr[dev] = ptr;
+    }
+    *out = g_static_work_ptr[dev];
+    return 0;
+}
+
+extern "C" int nlosb200_transient_static_work_ints(void) { return NLOS_STATIC_WORK_INTS; }
+
+extern "C" int nlosb200_transient_forward_static(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
+                                                 const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes,
+                                                 int cls, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT,
+                                                 float mcut, int mode, int variant, int one_pass, int accumulate, const float* sh, int sh_dim,
+                                                 int sh_degree, float* H, int cls2, int one_pass2, float* H2, void* stream)
+{
+    const long long need = (long long)n_tiles * (cls2 >= 0 ? 2 : 1);
+    NLOS_REQUIRE(n_tiles > 0 && need <= NLOS_STATIC_WORK_INTS,
+                 "transient_forward_static: %lld slice counters needed (n_tiles=%d x %d classes per launch) > the %d of the static scratch; "
+                 "use nlosb200_transient_forward with a caller buffer", need, n_tiles, cls2 >= 0 ? 2 : 1, NLOS_STATIC_WORK_INTS);
+    int* work = nullptr;
+    int rc = static_work_address(&work);
+    if (rc) return rc;
+    // (the launch clears the counters it uses with a stream-ordered memset, so the contents the last call left do not matter)
+    return nlosb200_transient_forward(tiles, n_tiles, A, records, N, list, list_bins, list_capacity, cell_offsets, n_classes, cls, work, t0, dt, T,
+                                      window, bucket, slice_len, c_deltaT, mcut, mode, variant, one_pass, accumulate, sh, sh_dim, sh_degree, H, cls2,
+                                      one_pass2, H2, nullptr, stream);
+}
+
 extern "C" int nlosb200_transient_backward(const float* tiles, int n_tiles, int A, const float* records, int N, const int* list,
                                            const int* list_bins, long long list_capacity, const long long* cell_offsets, int n_classes, int cls,
                                            int* work, float t0, float dt, int T, int window, int bucket, int slice_len, float c_deltaT, float mcut,
