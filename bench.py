@@ -135,12 +135,16 @@ def ncu_traffic(cfg, mode):
                 rd = vals
             else:
                 wr = vals
-    best, tot = -1.0, None
-    for i, n in enumerate(names):
-        is_bwd = ", 1, " in n or ", 1>" in n                 # transient[_narrow]_kernel<MODE, BWD = 1, SH>
-        if is_bwd and i < len(dur) and i < len(rd) and i < len(wr) and dur[i] == dur[i] and rd[i] == rd[i] and dur[i] > best:
-            best, tot = dur[i], rd[i] + (wr[i] if wr[i] == wr[i] else 0.0)
-    return tot, os.path.basename(path)
+    tag = os.path.basename(path)
+    for want_bwd in (True, False):                               # (a capture whose backward counters came back NaN: the dominant forward launch, labelled)
+        best, tot = -1.0, None
+        for i, n in enumerate(names):
+            is_bwd = ", 1, " in n or ", 1>" in n                 # transient[_narrow]_kernel<MODE, BWD = 1, SH>
+            if is_bwd == want_bwd and i < len(dur) and i < len(rd) and i < len(wr) and dur[i] == dur[i] and rd[i] == rd[i] and dur[i] > best:
+                best, tot = dur[i], rd[i] + (wr[i] if wr[i] == wr[i] else 0.0)
+        if tot is not None:
+            return tot, tag + ("" if want_bwd else ": dominant FORWARD launch (the backward's dram counters are NaN in this capture)")
+    return None, tag
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -454,7 +458,8 @@ def run_b200(args):
         hbm_view = {"algorithmic_bytes_per_launch": alg_bytes, "algorithmic_gbs": alg_bytes / (bwd_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                     "peak_source": hbm_src}
         if traffic:
-            hbm_view.update({"achieved": traffic / (bwd_ms * 1e-3) / 1e9, "frac": traffic / (bwd_ms * 1e-3) / 1e9 / hbm_peak, "bytes_per_launch": traffic})
+            t_ms = fwd_ms if "FORWARD" in (ttag or "") else bwd_ms       # (the pass the captured launch belongs to)
+            hbm_view.update({"achieved": traffic / (t_ms * 1e-3) / 1e9, "frac": traffic / (t_ms * 1e-3) / 1e9 / hbm_peak, "bytes_per_launch": traffic})
         n_bytes = N * 12 * 4
         n_cls = len(rnd._launch_groups())        # one launch per kernel variant (its entry classes are segments of the launch)
         n_flt = 1 if rnd.one_pass else 0
