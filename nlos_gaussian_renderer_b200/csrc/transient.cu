@@ -270,13 +270,13 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_kernel(const T
                             float rmax = sqrtf(bx * bx + by * by);
                             float thlo = atan2_fast(hiz > 0.f ? rmin : rmax, hiz);
                             float thhi = atan2_fast(loz > 0.f ? rmax : rmin, loz);
-                            i0 = clamp_ceil((thlo - th0) * idth - 0.02f, 0, A);
-                            i1 = clamp_floor((thhi - th0) * idth + 0.02f, -1, A - 1);
+                            i0 = lattice_lo((thlo - th0) * idth - 0.02f, A);
+                            i1 = lattice_hi((thhi - th0) * idth + 0.02f, A - 1);
                             if (loy > 0.f) {
                                 float phhi = atan2_fast(lox > 0.f ? hiy : loy, lox);
                                 float phlo = atan2_fast(hix > 0.f ? loy : hiy, hix);
-                                j0 = clamp_ceil((phlo - ph0) * idph - 0.02f, 0, A);
-                                j1 = clamp_floor((phhi - ph0) * idph + 0.02f, -1, A - 1);
+                                j0 = lattice_lo((phlo - ph0) * idph - 0.02f, A);
+                                j1 = lattice_hi((phhi - ph0) * idph + 0.02f, A - 1);
                             }
                         }
                         // ---- the pair's centre bin: up bins kc + s (s < n_up), down bins kc - 1 - s (s < n_dn).  For a Gaussian split

@@ -268,14 +268,14 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                             const float acx = fabsf(cx), acy = fabsf(cy);
                             const float thc = atan2_fast(rho, cz);
                             const float eth = fmaf(fmaf(fabsf(cz) * irho, fmaf(acx, v6.x, acy * v6.y), rho * v6.z), rcp_approx(d2) * 1.0001f, mg);
-                            i0 = clamp_ceil((thc - eth - th0) * idth - 0.02f, 0, A);
-                            i1 = clamp_floor((thc + eth - th0) * idth + 0.02f, -1, A - 1);
+                            i0 = lattice_lo((thc - eth - th0) * idth - 0.02f, A);
+                            i1 = lattice_hi((thc + eth - th0) * idth + 0.02f, A - 1);
                             if (loy > 0.f) {
                                 const float ph0 = s_pi[PI_PH0 * 32 + lane], idph = s_pi[PI_IDPH * 32 + lane];
                                 const float phc = atan2_fast(cy, cx);
                                 const float eph = fmaf(fmaf(acy, v6.x, acx * v6.y), irho * irho * 1.0001f, mg);
-                                j0 = clamp_ceil((phc - eph - ph0) * idph - 0.02f, 0, A);
-                                j1 = clamp_floor((phc + eph - ph0) * idph + 0.02f, -1, A - 1);
+                                j0 = lattice_lo((phc - eph - ph0) * idph - 0.02f, A);
+                                j1 = lattice_hi((phc + eph - ph0) * idph + 0.02f, A - 1);
                             }
                         }
                     }
