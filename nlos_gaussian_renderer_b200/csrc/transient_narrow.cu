@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     // ---- the pair's centre bin: up bins kc + s (s < n_up), down bins kc - 1 - s (s < n_dn).  For a Gaussian split
                     //      over several entries kc is aligned to s_lo modulo 4, so that the entry's boundaries fall on the
                     //      4-step blocks of the backward loop (L % 4 == 0: exact clipping at no cost in the hot loop)
-                    int kc = (int)rintf(fminf(fmaxf((D - t0) * inv_dt, fRlo), fRhi + 1.0f));
+                    int kc = rint_small(fminf(fmaxf((D - t0) * inv_dt, fRlo), fRhi + 1.0f));      // (0 <= value <= T: exact rint without F2I)
                     if (split) {
                         kc = s_lo + ((kc - s_lo + 2) & ~3);
                         if (kc > s_hi + 1) kc -= 4;

@@ -72,6 +72,10 @@ __device__ __forceinline__ int clamp_floor(float x, int lo, int hi)
 // Conservative lattice-index bounds of the footprint rectangle without FRND / F2I (both quarter-rate XU instructions; the four clamps of a pair
 // were 4.7 % of the narrow forward's stall samples): rint by the 1.5 * 2^23 trick.  lattice_lo(x) <= ceil(x) and lattice_hi(y) >= floor(y)
 // (equal unless x is within 0.01 above / y within 0.01 below an integer: one more candidate row or column, decided by the slab test as ever).
+__device__ __forceinline__ int rint_small(float x)                    // (int)rintf(x) for |x| < 2^22, NaN -> garbage: callers clamp first
+{
+    return __float_as_int(__fadd_rn(x, 12582912.0f)) - 0x4B400000;
+}
 __device__ __forceinline__ int lattice_lo(float x, int hi)            // in [0, hi]
 {
     x = fminf(fmaxf(x, 0.f), (float)hi) + 0.49f;
