@@ -243,6 +243,25 @@ __device__ __forceinline__ float atan2_fast(float y, float x)
     return y < 0.f ? -r : r;
 }
 
+// atan2(y, x) for y > 0 with inv_y ~ 1 / y known: the same polynomial; the reciprocal that is still needed (of |x|, when |x| > y) does not depend
+// on y, so it is off the dependency chain  sum of squares -> rsqrt -> y  of the caller
+__device__ __forceinline__ float atan2_fast_inv(float y, float x, float inv_y)
+{
+    const float ax = fabsf(x);
+    const bool steep = y >= ax;
+    const float a = steep ? ax * inv_y : y * rcp_approx(fmaxf(ax, 1e-30f));
+    const float s = a * a;
+    float p = -0.01172120f;
+    p = fmaf(p, s, 0.05265332f);
+    p = fmaf(p, s, -0.11643287f);
+    p = fmaf(p, s, 0.19354346f);
+    p = fmaf(p, s, -0.33262347f);
+    p = fmaf(p, s, 0.99997726f);
+    float r = p * a;
+    if (steep) r = 1.57079632679f - r;
+    return x < 0.f ? 3.14159265359f - r : r;
+}
+
 // erf with |abs error| <= ~1.2e-7 : odd polynomial for |x|<1 , 1-exp(poly) beyond (CUDA-libm style split)
 __device__ __forceinline__ float erf_fast(float x)
 {

@@ -233,7 +233,10 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                     // numerical backward: the same sums with ray 0 / ray 1 of an iteration in the two halves of packed registers
                     f32x2 pga[3] = {0ull, 0ull, 0ull}, pg[9] = {0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull, 0ull}, pgwa = 0ull;
                     // ---- the pair (this lane's scan point): radial reject against the entry's bins, AABB relative to the scan point, a = M (o - mu)
-                    const float D = sqrtf(d2);
+                    // D = |mu - o| to ~1 ulp from ONE MUFU.RSQ + a Newton step (no IEEE-sqrt slow path); 1 / d2 for the footprint below is ir^2
+                    const float ir = rsqrt_approx(fmaxf(d2, 1e-30f));
+                    float D = d2 * ir;
+                    D = fmaf(fmaf(-D, D, d2), 0.5f * ir, D);
                     float alb = v4.w;                                                                       // degree-0 albedo of the record
                     if (SH)                                                                                 // view-dependent: one albedo per (Gaussian, scan point)
                         alb = sh_pair_albedo(P.sh + (size_t)(ent & ((1u << NLOS_ENTRY_SHIFT) - 1u)) * P.sh_dim, P.sh_degree, cx, cy, cz, D);
@@ -264,10 +267,12 @@ __global__ void __launch_bounds__(TR_WPB * 32, TR_MINB) transient_narrow_kernel(
                         const float irho = rsqrt_approx(fmaxf(rho2, 1e-30f)), rho = rho2 * irho, rmin = rho - Rb;
                         if (fast && rmin > 0.5f * rho) {
                             const float th0 = s_pi[PI_TH0 * 32 + lane], idth = s_pi[PI_IDTH * 32 + lane];
-                            const float mg = Rb * Rb * rcp_approx(rmin * rmin);
+                            // Rb^2 / rmin^2 = x^2 / (1 - x)^2, x = Rb / rho < 1/2, bounded by x^2 (1 + 2x + 12x^2): no reciprocal on the chain
+                            const float xr = Rb * irho;
+                            const float mg = xr * xr * fmaf(xr, fmaf(12.0f, xr, 2.0f), 1.0f);
                             const float acx = fabsf(cx), acy = fabsf(cy);
-                            const float thc = atan2_fast(rho, cz);
-                            const float eth = fmaf(fmaf(fabsf(cz) * irho, fmaf(acx, v6.x, acy * v6.y), rho * v6.z), rcp_approx(d2) * 1.0001f, mg);
+                            const float thc = atan2_fast_inv(rho, cz, irho);
+                            const float eth = fmaf(fmaf(fabsf(cz) * irho, fmaf(acx, v6.x, acy * v6.y), rho * v6.z), ir * ir * 1.0001f, mg);
                             i0 = lattice_lo((thc - eth - th0) * idth - 0.02f, A);
                             i1 = lattice_hi((thc + eth - th0) * idth + 0.02f, A - 1);
                             if (loy > 0.f) {
